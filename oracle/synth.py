@@ -1,0 +1,123 @@
+"""Seeded synthetic inputs and weights.
+
+Test infrastructure.  Pure torch-CPU, no dependency on /root/reference, so the
+same bytes are regenerated on the GPU box.
+
+* ``make_pair``       one registration pair of correspondences with a known
+                      rigid motion, the shape the reference's datasets produce
+                      (``datasets/ThreeDMatch.py:300-310``: corr_pos is the
+                      concatenated src/tgt keypoints minus their mean).
+* ``make_state_dict`` a state_dict in the reference's key layout
+                      (``models/PointDSC.py:92-121``; 358 entries at L=12),
+                      xavier-normal conv weights like the reference constructor
+                      but with non-trivial biases and BatchNorm running stats so
+                      BN is not the identity.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+
+import torch
+
+CONFIGS = {
+    # name: N, inlier_ratio, scale, noise, sigma_d, inlier_threshold, nms_radius
+    "3dmatch": dict(inlier_ratio=0.10, scale=3.0, noise=0.02, sigma_d=0.10,
+                    inlier_threshold=0.10, nms_radius=0.10),
+    "kitti": dict(inlier_ratio=0.05, scale=50.0, noise=0.1, sigma_d=1.2,
+                  inlier_threshold=0.6, nms_radius=0.6),
+}
+
+
+def random_rotation(gen: torch.Generator) -> torch.Tensor:
+    a = torch.randn(3, 3, generator=gen, dtype=torch.float64)
+    q, r = torch.linalg.qr(a)
+    q = q * torch.sign(torch.diagonal(r))[None, :]
+    if torch.det(q) < 0:
+        q[:, 2] = -q[:, 2]
+    return q.float()
+
+
+def make_pair(seed: int, N: int, inlier_ratio: float = 0.10, scale: float = 3.0,
+              noise: float = 0.02, **_unused):
+    """Returns dict(corr_pos [1,N,6], src_keypts [1,N,3], tgt_keypts [1,N,3],
+    gt_trans [4,4], gt_labels [N]) fp32, CPU."""
+    gen = torch.Generator().manual_seed(int(seed))
+    src = torch.rand(N, 3, generator=gen) * scale
+    R = random_rotation(gen)
+    t = torch.randn(3, generator=gen) * (scale / 3.0)
+    n_in = int(N * inlier_ratio)
+    tgt = torch.rand(N, 3, generator=gen) * scale + t
+    perm = torch.randperm(N, generator=gen)
+    inl = perm[:n_in]
+    tgt[inl] = src[inl] @ R.T + t + torch.randn(n_in, 3, generator=gen) * noise
+    labels = torch.zeros(N)
+    labels[inl] = 1.0
+    corr = torch.cat([src, tgt], dim=-1)
+    corr = corr - corr.mean(dim=0, keepdim=True)
+    T = torch.eye(4)
+    T[:3, :3] = R
+    T[:3, 3] = t
+    return {
+        "corr_pos": corr[None].contiguous(),
+        "src_keypts": src[None].contiguous(),
+        "tgt_keypts": tgt[None].contiguous(),
+        "gt_trans": T,
+        "gt_labels": labels,
+    }
+
+
+def make_batch(seeds, N: int, **kw):
+    pairs = [make_pair(s, N, **kw) for s in seeds]
+    out = {k: torch.cat([p[k] for p in pairs], dim=0)
+           for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    out["gt_trans"] = torch.stack([p["gt_trans"] for p in pairs])
+    out["gt_labels"] = torch.stack([p["gt_labels"] for p in pairs])
+    return out
+
+
+def _xavier(gen, out_c, in_c):
+    std = math.sqrt(2.0 / float(in_c + out_c))
+    return torch.randn(out_c, in_c, 1, generator=gen) * std
+
+
+def make_state_dict(seed: int = 1234, in_dim: int = 6, num_layers: int = 12,
+                    num_channels: int = 128, sigma: float = 1.0,
+                    sigma_d: float = 0.10) -> "OrderedDict[str, torch.Tensor]":
+    """Key order and shapes follow the reference module tree
+    (``models/PointDSC.py:12-23,54-63,97-113``)."""
+    gen = torch.Generator().manual_seed(int(seed))
+    C = num_channels
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+
+    def conv(prefix, out_c, in_c):
+        sd[prefix + ".weight"] = _xavier(gen, out_c, in_c)
+        sd[prefix + ".bias"] = torch.randn(out_c, generator=gen) * 0.05
+
+    def bn(prefix, c):
+        sd[prefix + ".weight"] = 1.0 + 0.1 * torch.randn(c, generator=gen)
+        sd[prefix + ".bias"] = 0.05 * torch.randn(c, generator=gen)
+        sd[prefix + ".running_mean"] = 0.1 * torch.randn(c, generator=gen)
+        sd[prefix + ".running_var"] = 0.5 + torch.rand(c, generator=gen)
+        sd[prefix + ".num_batches_tracked"] = torch.tensor(100, dtype=torch.long)
+
+    sd["sigma"] = torch.tensor([sigma], dtype=torch.float32)
+    sd["sigma_spat"] = torch.tensor([sigma_d], dtype=torch.float32)
+    for i in range(num_layers):
+        p = f"encoder.blocks.PointCN_layer_{i}"
+        conv(p + ".0", C, C)
+        bn(p + ".1", C)
+        q = f"encoder.blocks.NonLocal_layer_{i}"
+        conv(q + ".fc_message.0", C // 2, C)
+        bn(q + ".fc_message.1", C // 2)
+        conv(q + ".fc_message.3", C // 2, C // 2)
+        bn(q + ".fc_message.4", C // 2)
+        conv(q + ".fc_message.6", C, C // 2)
+        conv(q + ".projection_q", C, C)
+        conv(q + ".projection_k", C, C)
+        conv(q + ".projection_v", C, C)
+    conv("encoder.layer0", C, in_dim)
+    conv("classification.0", 32, C)
+    conv("classification.2", 32, 32)
+    conv("classification.4", 1, 32)
+    return sd

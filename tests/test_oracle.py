@@ -1,0 +1,83 @@
+"""Pins the CPU oracle (oracle/restate.py) against golden vectors produced by the
+UNMODIFIED reference (oracle/gen_golden.py ran /root/reference/models/PointDSC.py).
+The reference has no tests of its own; running it is the pin."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN_CASES, load_golden
+from oracle import restate, synth
+
+
+def _run_oracle(meta, g):
+    fam = synth.CONFIGS[meta["family"]]
+    sd = synth.make_state_dict(meta["weight_seed"], num_layers=meta["num_layers"], sigma_d=fam["sigma_d"])
+    ctor = meta["ctor"]
+    return restate.forward_pair(sd, g["corr_pos"], g["src_keypts"], g["tgt_keypts"],
+                                num_layers=ctor["num_layers"], inlier_threshold=ctor["inlier_threshold"],
+                                nms_radius=ctor["nms_radius"])
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_inputs_regenerate(case):
+    """The seeded generator reproduces the committed inputs bit for bit."""
+    meta, g = load_golden(case)
+    p = synth.make_pair(meta["pair_seed"], meta["N"], **synth.CONFIGS[meta["family"]])
+    for k in ("corr_pos", "src_keypts", "tgt_keypts"):
+        assert torch.equal(p[k], g[k]), k
+
+
+@pytest.mark.parametrize("case", [c for c in GOLDEN_CASES if "n2000" not in c])
+def test_oracle_matches_reference_golden(case):
+    meta, g = load_golden(case)
+    out = _run_oracle(meta, g)
+    # floating point: same torch build -> same bits; allow a hair for other BLAS builds
+    for k, tol in [("confidence", 1e-5), ("normed_features", 1e-5), ("seed_trans", 1e-4),
+                   ("seed_fitness", 0), ("final_trans", 1e-5), ("initial_trans", 1e-4)]:
+        a, b = out[k].float(), g[k].float()
+        assert a.shape == b.shape, k
+        assert (a - b).abs().max().item() <= tol, (k, (a - b).abs().max().item())
+    # integer / index outputs: bit exact
+    assert torch.equal(out["seeds"], g["seeds"])
+    assert torch.equal(out["knn_idx"], g["knn_idx"])
+    assert torch.equal(out["final_labels"], g["final_labels"])
+    # post refinement: sizes of the inlier sets the reference refitted on
+    ref_sizes = g["refine_sizes"].tolist()
+    assert out["refine_counts"][:len(ref_sizes)] == ref_sizes
+    assert len(out["refine_counts"]) in (len(ref_sizes) + 1, 20)
+
+
+def test_power_iteration_known_answer():
+    """Known-answer test in the spirit of misc/eigen.py:9-45: power iteration on random
+    symmetric non-negative matrices converges to the eigh leading eigenvector."""
+    g = torch.Generator().manual_seed(5)
+    A = torch.rand(16, 40, 40, generator=g)
+    A = (A + A.transpose(1, 2)) / 2
+    A[:, torch.arange(40), torch.arange(40)] = 0
+    v, used = restate.leading_eigenvector(A, 200)
+    w, V = np.linalg.eigh(A.double().numpy())
+    lead = torch.from_numpy(V[:, :, -1]).float()
+    lead = lead * torch.sign(lead.sum(-1, keepdim=True))
+    assert used < 200
+    assert (v / v.norm(dim=-1, keepdim=True) - lead).abs().max() < 1e-4
+
+
+def test_kabsch_recovers_exact_motion():
+    g = torch.Generator().manual_seed(3)
+    A = torch.rand(4, 50, 3, generator=g)
+    R = torch.stack([synth.random_rotation(g) for _ in range(4)])
+    t = torch.randn(4, 3, 1, generator=g)
+    B = (R @ A.permute(0, 2, 1) + t).permute(0, 2, 1)
+    w = torch.rand(4, 50, generator=g)
+    T, _ = restate.rigid_transform_3d(A, B, w)
+    assert (T[:, :3, :3] - R).abs().max() < 1e-5
+    assert (T[:, :3, 3:4] - t).abs().max() < 1e-5
+
+
+def test_full_power_iteration_inliers_dominate():
+    """R7b: the leading eigenvector of the full compatibility matrix puts its mass on the
+    mutually consistent (inlier) correspondences."""
+    p = synth.make_pair(1, 400, **synth.CONFIGS["3dmatch"])
+    v, used = restate.power_iteration_full(p["src_keypts"], p["tgt_keypts"], torch.tensor([0.1]), 10)
+    top = torch.argsort(v[0], descending=True)[:20]
+    assert p["gt_labels"][top].mean() > 0.9
