@@ -1,0 +1,148 @@
+/*
+ * pointdsc_b200 -- C ABI of the B200 (sm_100a) kernels behind PointDSC.forward(data).
+ *
+ * The reference (AmnonDrory/PointDSC) is pure Python/PyTorch and has no FFI: the interface
+ * this library replaces is the set of Python methods listed beside each entry point
+ * (file:line relative to the reference checkout).  A maintainer binds these symbols with
+ * ctypes (INTEGRATION.md shows the stub); pointdsc_b200/_cabi.py is that binding.
+ *
+ * Conventions
+ *  - Every pointer is a DEVICE pointer owned by the caller (inputs, outputs and workspace).
+ *    Kernels never allocate or free and keep no pointer after return.
+ *  - Tensors are dense row-major: keypoints [B,N,3] fp32, features [B,N,C] fp32 (channel last),
+ *    transforms [B,S,4,4] fp32, indices int64 (what torch produces), counts int32.
+ *  - Work is enqueued on `stream` (a cudaStream_t passed as void*), asynchronously; no
+ *    device-wide synchronisation inside.  Reentrant across host threads/streams/devices.
+ *  - Return value: PDSC_OK or an error code; pdsc_last_error() gives the message for the
+ *    calling thread.  There is no CPU fallback anywhere.
+ *  - B independent registration pairs per call (the reference's test path is batch-size 1,
+ *    models/PointDSC.py:210,414; B>1 means B independent runs of it).
+ */
+#ifndef POINTDSC_B200_H
+#define POINTDSC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDSC_OK 0
+#define PDSC_ERR_ARG 1         /* bad shape / null pointer / alignment */
+#define PDSC_ERR_DEVICE 2      /* not an sm_100 device */
+#define PDSC_ERR_CUDA 3        /* launch or runtime error, see pdsc_last_error */
+#define PDSC_ERR_WORKSPACE 4   /* workspace too small */
+
+/* precision modes of pdsc_nonlocal_attn */
+#define PDSC_ATTN_FP32 0       /* CUDA-core fp32 FMA contractions (exact reference arithmetic) */
+#define PDSC_ATTN_SPLIT16 1    /* tcgen05 fp16 hi/lo split, 3 MMAs per contraction, fp32 accumulate in TMEM */
+#define PDSC_ATTN_FP16 2       /* tcgen05 single-pass fp16 (fast, outside the parity tolerance) */
+
+/* operations for pdsc_workspace_bytes */
+#define PDSC_OP_NONLOCAL_ATTN 1
+#define PDSC_OP_PICK_SEEDS 2
+#define PDSC_OP_SEED_KNN 3
+#define PDSC_OP_SEED_HYPOTHESES 4
+#define PDSC_OP_SCORE_HYPOTHESES 5
+#define PDSC_OP_POST_REFINE 6
+#define PDSC_OP_POWER_ITER_FULL 7
+
+int pdsc_version(void);
+const char* pdsc_last_error(void);
+/* Number of CUDA kernels this library has enqueued in this process (all threads). */
+uint64_t pdsc_launch_count(void);
+/* 0 when the current device is sm_100 (B200); PDSC_ERR_DEVICE otherwise */
+int pdsc_check_device(void);
+/* Bytes of caller-provided workspace an operation needs (256-byte aligned base expected).
+ * `mode` is the attention precision mode for PDSC_OP_NONLOCAL_ATTN, else ignored. */
+size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode);
+
+/* (a) compatibility-weighted non-local attention; replaces
+ *     models/PointDSC.py:150-153 (src_dist / corr_compatibility, never materialised) and
+ *     NonLocalBlock.forward models/PointDSC.py:39-42 (QK^T/sqrt(C), softmax(compat*logits), PV).
+ *  q,k,v: [B,N,C] fp32 with row stride ld_qkv floats (they may be slices of one [B,N,3C]
+ *  projection output); src,tgt: [B,N,3]; out: message [B,N,C] fp32, row stride ld_out.
+ *  sigma_spat is the fp32 parameter value; compat = max(0, 1 - (|si-sj|-|ti-tj|)^2 / sigma_spat^2). */
+int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t ld_qkv,
+                       const float* src, const float* tgt, float* out, int64_t ld_out,
+                       int B, int N, int C, float sigma_spat, int mode,
+                       void* ws, size_t ws_bytes, void* stream);
+
+/* (c) NMS seed picking; replaces PointDSC.pick_seeds models/PointDSC.py:199-217.
+ *  is_local_max[i] = all_j (score_i >= score_j  or  |s_i-s_j| >= R);
+ *  seeds = first S indices ordered by (score*is_local_max descending, index ascending).
+ *  The reference's order among equal keys is unspecified (torch.argsort); ours is by index.
+ *  seeds_out int64 [B,S]; is_local_max_out uint8 [B,N] (nullable); n_pos_out int32 [B]
+ *  (nullable) = number of strictly positive keys (the prefix whose order is well defined). */
+int pdsc_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S,
+                    int64_t* seeds_out, uint8_t* is_local_max_out, int32_t* n_pos_out,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* (c) feature-space kNN of the seed rows; replaces knn() models/common.py:48-69 as called at
+ *  models/PointDSC.py:251-252 (ignore_self, normalized features) but only for the S seed rows.
+ *  dist = 2 - 2 f_s.f_j; the k nearest j != s ordered by (dist ascending, index ascending).
+ *  knn_idx_out int64 [B,S,k]; knn_dist_out fp32 [B,S,k] (nullable). */
+int pdsc_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int C, int S, int k,
+                  int64_t* knn_idx_out, float* knn_dist_out,
+                  void* ws, size_t ws_bytes, void* stream);
+
+/* (d) per-seed local spectral matching + weighted Kabsch; replaces
+ *  cal_seed_trans models/PointDSC.py:257-320, cal_leading_eigenvector :338-358 and
+ *  rigid_transform_3d models/common.py:7-45 (3x3 SVD on device, no host round trip).
+ *  sigma = learned feature bandwidth (self.sigma), sigma_spat = self.sigma_spat.
+ *  The power iteration keeps the reference's stopping rule: all seeds of a pair stop at the
+ *  first iteration where torch.allclose(v, v_last) holds over the whole [S,k] tensor.
+ *  seed_trans_out fp32 [B,S,4,4]; weights_out fp32 [B,S,k] (nullable, normalised weights);
+ *  iters_out int32 [B] (nullable, iterations used). */
+int pdsc_seed_hypotheses(const float* normed, const float* src, const float* tgt,
+                         const int64_t* knn_idx, int B, int N, int C, int S, int k,
+                         float sigma, float sigma_spat, int num_iterations,
+                         float* seed_trans_out, float* weights_out, int32_t* iters_out,
+                         void* ws, size_t ws_bytes, void* stream);
+
+/* (e) hypothesis scoring; replaces models/PointDSC.py:325-335.
+ *  inlier_count[s] = #{n : |R_s src_n + t_s - tgt_n| < thr}; best = first argmax;
+ *  final_trans = seed_trans[best]; final_labels = 0/1 fp32 mask under the best transform.
+ *  inlier_count_out int32 [B,S]; best_idx_out int64 [B]; final_trans_out fp32 [B,4,4];
+ *  final_labels_out fp32 [B,N]. */
+int pdsc_score_hypotheses(const float* seed_trans, const float* src, const float* tgt,
+                          int B, int N, int S, float thr,
+                          int32_t* inlier_count_out, int64_t* best_idx_out,
+                          float* final_trans_out, float* final_labels_out,
+                          void* ws, size_t ws_bytes, void* stream);
+
+/* (e) post refinement; replaces PointDSC.post_refinement models/PointDSC.py:403-438
+ *  (+ transform utils/SE3.py:43-57, rigid_transform_3d models/common.py:7-45).
+ *  Up to max_iter rounds of: d=|T src - tgt|, mask=d<tau, stop when the inlier count repeats,
+ *  else refit T on the masked points with weights 1/(1+(d/tau)^2).  The whole loop runs on the
+ *  device.  trans_inout fp32 [B,4,4]; iters_out int32 [B] (nullable; number of refits);
+ *  counts_out int32 [B,max_iter] (nullable; inlier count seen at each round, -1 = not run). */
+int pdsc_post_refine(float* trans_inout, const float* src, const float* tgt, int B, int N,
+                     float tau, int max_iter, int32_t* iters_out, int32_t* counts_out,
+                     void* stream);
+
+/* (b) full-matrix power iteration building block; cal_leading_eigenvector
+ *  models/PointDSC.py:338-358 applied to the N x N compatibility matrix with zero diagonal
+ *  (the call kept at models/PointDSC.py:170; baseline_scripts/baseline_3DMatch.py:19-46).
+ *  The matrix is recomputed on the fly, never stored.
+ *  pdsc_compat_matvec: y[r-row_begin] = sum_{j!=r} compat(r,j) v[j] for row_begin<=r<row_end
+ *  (row sharding for multi-GPU: every rank owns a row range, then all-gathers y).
+ *  pdsc_power_normalize: v_new = y/(|y|+1e-6); sets *converged_flag (int32, device) when
+ *  allclose(v_new, v_last, rtol 1e-5, atol 1e-8); when the flag was already set on entry it
+ *  leaves v unchanged (device-side early exit, no host sync).  iters_done is incremented
+ *  on the device for every executed iteration.
+ *  pdsc_power_iter_full: single-GPU driver, num_iterations launches of the pair above. */
+int pdsc_compat_matvec(const float* src, const float* tgt, const float* v, float* y,
+                       int N, int row_begin, int row_end, float sigma_spat,
+                       const int32_t* converged_flag, void* stream);
+int pdsc_power_normalize(const float* y, float* v_inout, int N, int32_t* converged_flag,
+                         int32_t* iters_done, void* ws, size_t ws_bytes, void* stream);
+int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N,
+                         float sigma_spat, int num_iterations, int32_t* iters_out,
+                         void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POINTDSC_B200_H */

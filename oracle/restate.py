@@ -298,8 +298,11 @@ def power_iteration_full(src, tgt, sigma_spat, num_iterations):
 # metrics used by the parity tests  (libs/loss.py:44-49)
 # --------------------------------------------------------------------------
 def rotation_error_deg(Ra, Rb):
-    tr = torch.diagonal(Ra.double().transpose(-1, -2) @ Rb.double(), dim1=-2, dim2=-1).sum(-1)
-    return torch.rad2deg(torch.acos(torch.clamp((tr - 1) / 2, -1, 1)))
+    """Angle between two rotations.  For rotations ||Ra-Rb||_F = 2*sqrt(2)*sin(angle/2); this
+    form stays accurate near zero, where the trace/acos form of libs/loss.py:44-46 loses all
+    digits in fp32 (acos(1-1e-7) is already 0.026 deg)."""
+    d = torch.linalg.matrix_norm(Ra.double() - Rb.double())
+    return torch.rad2deg(2 * torch.asin(torch.clamp(d / (2 * 2 ** 0.5), max=1.0)))
 
 
 def translation_error(ta, tb):

@@ -1,0 +1,265 @@
+"""ctypes binding of libpointdsc_b200.so (include/pointdsc_b200.h).
+
+This is the stub a maintainer of the reference would add: raw device
+pointers and sizes in, an int status out; torch only supplies ``data_ptr()`` and the
+current stream.  There is no CPU fallback: a missing library or a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int64, c_size_t, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
+
+ATTN_FP32, ATTN_SPLIT16, ATTN_FP16 = 0, 1, 2
+OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
+OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
+
+# name -> (restype, argtypes); must list every symbol the header declares
+SIGNATURES = {
+    "pdsc_version": (c_int, []),
+    "pdsc_last_error": (ctypes.c_char_p, []),
+    "pdsc_check_device": (c_int, []),
+    "pdsc_launch_count": (ctypes.c_uint64, []),
+    "pdsc_workspace_bytes": (c_size_t, [c_int] * 7),
+    "pdsc_nonlocal_attn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
+                                   c_int, c_int, c_int, c_float, c_int, c_void_p, c_size_t, c_void_p]),
+    "pdsc_pick_seeds": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p,
+                                c_void_p, c_size_t, c_void_p]),
+    "pdsc_seed_knn": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                              c_void_p, c_size_t, c_void_p]),
+    "pdsc_seed_hypotheses": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                     c_float, c_float, c_int, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_size_t, c_void_p]),
+    "pdsc_score_hypotheses": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_post_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
+                                 c_void_p]),
+    "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
+                                   c_void_p, c_void_p]),
+    "pdsc_power_normalize": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
+                                     c_void_p, c_size_t, c_void_p]),
+}
+
+_lib = None
+launch_count = 0   # kernels-launching C-ABI calls made through this binding (bench.py reports it)
+
+
+def load():
+    """Loads the shared library (no CUDA context needed) and declares every signature."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m pointdsc_b200.build` "
+                "(there is no CPU or PyTorch fallback for the CUDA path)")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = load().pdsc_last_error().decode(errors="replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+def _ptr(t, dtype=None, name="tensor"):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (pointdsc_b200 has no CPU path)")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Workspace:
+    """Caller-owned scratch: grows on demand, reused across calls on one device."""
+
+    def __init__(self):
+        self.buf = None
+
+    def get(self, nbytes, device):
+        nbytes = max(int(nbytes), 256)
+        if self.buf is None or self.buf.numel() < nbytes or self.buf.device != device:
+            self.buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        return self.buf
+
+
+_default_ws = {}
+
+
+def _ws(nbytes, device, ws):
+    if ws is None:
+        ws = _default_ws.setdefault(device, Workspace())
+    return ws.get(nbytes, device)
+
+
+def workspace_bytes(op, B=1, N=0, C=128, S=0, k=0, mode=0):
+    return int(load().pdsc_workspace_bytes(op, B, N, C, S, k, mode))
+
+
+def kernel_launches():
+    """CUDA kernels enqueued by the library so far (counted inside the library)."""
+    return int(load().pdsc_launch_count())
+
+
+def check_device():
+    _check(load().pdsc_check_device(), "pdsc_check_device")
+
+
+def _count():
+    global launch_count
+    launch_count += 1
+
+
+# ------------------------------------------------------------------------------------------------
+def nonlocal_attn(q, k, v, src, tgt, sigma_spat, mode=ATTN_FP32, out=None, ws=None):
+    """q,k,v: [B,N,C] fp32 views with a common row stride (e.g. slices of a [B,N,3C] tensor)."""
+    lib = load()
+    B, N, C = q.shape
+    for t in (q, k, v):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.stride(2) == 1 and t.stride(0) == N * t.stride(1)
+                and t.stride(1) == q.stride(1) and t.shape == q.shape):
+            raise RuntimeError("q,k,v must be CUDA fp32 [B,N,C] with unit channel stride and equal row stride")
+    if out is None:
+        out = torch.empty(B, N, C, dtype=torch.float32, device=q.device)
+    nbytes = workspace_bytes(OP_NONLOCAL_ATTN, B, N, C, mode=mode)
+    w = _ws(nbytes, q.device, ws)
+    rc = lib.pdsc_nonlocal_attn(q.data_ptr(), k.data_ptr(), v.data_ptr(), q.stride(1),
+                                _ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"),
+                                _ptr(out, torch.float32, "out"), out.stride(1), B, N, C, float(sigma_spat), int(mode),
+                                w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_nonlocal_attn")
+    _count()
+    return out
+
+
+def pick_seeds(src, scores, R, S, ws=None, want_aux=False):
+    lib = load()
+    B, N = scores.shape
+    seeds = torch.empty(B, S, dtype=torch.int64, device=scores.device)
+    lm = torch.empty(B, N, dtype=torch.uint8, device=scores.device) if want_aux else None
+    npos = torch.empty(B, dtype=torch.int32, device=scores.device) if want_aux else None
+    w = _ws(workspace_bytes(OP_PICK_SEEDS, B, N), scores.device, ws)
+    rc = lib.pdsc_pick_seeds(_ptr(src, torch.float32, "src"), _ptr(scores, torch.float32, "scores"), B, N, float(R), S,
+                             seeds.data_ptr(), _ptr(lm), _ptr(npos), w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_pick_seeds")
+    _count()
+    return (seeds, lm, npos) if want_aux else seeds
+
+
+def seed_knn(normed, seeds, k, ws=None, want_dist=False):
+    lib = load()
+    B, N, C = normed.shape
+    S = seeds.shape[1]
+    idx = torch.empty(B, S, k, dtype=torch.int64, device=normed.device)
+    dist = torch.empty(B, S, k, dtype=torch.float32, device=normed.device) if want_dist else None
+    w = _ws(workspace_bytes(OP_SEED_KNN, B, N, C, S, k), normed.device, ws)
+    rc = lib.pdsc_seed_knn(_ptr(normed, torch.float32, "normed"), _ptr(seeds, torch.int64, "seeds"), B, N, C, S, k,
+                           idx.data_ptr(), _ptr(dist), w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_seed_knn")
+    _count()
+    return (idx, dist) if want_dist else idx
+
+
+def seed_hypotheses(normed, src, tgt, knn_idx, sigma, sigma_spat, num_iterations, ws=None, want_aux=False):
+    lib = load()
+    B, N, C = normed.shape
+    S, k = knn_idx.shape[1], knn_idx.shape[2]
+    trans = torch.empty(B, S, 4, 4, dtype=torch.float32, device=normed.device)
+    weights = torch.empty(B, S, k, dtype=torch.float32, device=normed.device) if want_aux else None
+    iters = torch.empty(B, dtype=torch.int32, device=normed.device) if want_aux else None
+    w = _ws(workspace_bytes(OP_SEED_HYPOTHESES, B, N, C, S, k), normed.device, ws)
+    rc = lib.pdsc_seed_hypotheses(_ptr(normed, torch.float32, "normed"), _ptr(src, torch.float32, "src"),
+                                  _ptr(tgt, torch.float32, "tgt"), _ptr(knn_idx, torch.int64, "knn_idx"),
+                                  B, N, C, S, k, float(sigma), float(sigma_spat), int(num_iterations),
+                                  trans.data_ptr(), _ptr(weights), _ptr(iters), w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_seed_hypotheses")
+    _count()
+    return (trans, weights, iters) if want_aux else trans
+
+
+def score_hypotheses(seed_trans, src, tgt, thr):
+    lib = load()
+    B, S = seed_trans.shape[0], seed_trans.shape[1]
+    N = src.shape[1]
+    dev = src.device
+    counts = torch.empty(B, S, dtype=torch.int32, device=dev)
+    best = torch.empty(B, dtype=torch.int64, device=dev)
+    final_trans = torch.empty(B, 4, 4, dtype=torch.float32, device=dev)
+    labels = torch.empty(B, N, dtype=torch.float32, device=dev)
+    rc = lib.pdsc_score_hypotheses(_ptr(seed_trans, torch.float32, "seed_trans"), _ptr(src, torch.float32, "src"),
+                                   _ptr(tgt, torch.float32, "tgt"), B, N, S, float(thr), counts.data_ptr(),
+                                   best.data_ptr(), final_trans.data_ptr(), labels.data_ptr(), None, 0, _stream())
+    _check(rc, "pdsc_score_hypotheses")
+    _count()
+    return counts, best, final_trans, labels
+
+
+def post_refine(trans, src, tgt, tau, max_iter=20, want_aux=False):
+    """Refines ``trans`` [B,4,4] IN PLACE and returns it."""
+    lib = load()
+    B, N = src.shape[0], src.shape[1]
+    iters = torch.empty(B, dtype=torch.int32, device=src.device) if want_aux else None
+    counts = torch.empty(B, max_iter, dtype=torch.int32, device=src.device) if want_aux else None
+    rc = lib.pdsc_post_refine(_ptr(trans, torch.float32, "trans"), _ptr(src, torch.float32, "src"),
+                              _ptr(tgt, torch.float32, "tgt"), B, N, float(tau), int(max_iter), _ptr(iters),
+                              _ptr(counts), _stream())
+    _check(rc, "pdsc_post_refine")
+    _count()
+    return (trans, iters, counts) if want_aux else trans
+
+
+def compat_matvec(src, tgt, v, row_begin, row_end, sigma_spat, converged_flag=None, out=None):
+    """y = M[row_begin:row_end, :] v for one pair; src,tgt [N,3], v [N]."""
+    lib = load()
+    N = v.shape[0]
+    if out is None:
+        out = torch.empty(row_end - row_begin, dtype=torch.float32, device=v.device)
+    rc = lib.pdsc_compat_matvec(_ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"),
+                                _ptr(v, torch.float32, "v"), _ptr(out, torch.float32, "y"), N, int(row_begin),
+                                int(row_end), float(sigma_spat), _ptr(converged_flag), _stream())
+    _check(rc, "pdsc_compat_matvec")
+    _count()
+    return out
+
+
+def power_normalize(y, v, converged_flag, iters_done=None):
+    lib = load()
+    rc = lib.pdsc_power_normalize(_ptr(y, torch.float32, "y"), _ptr(v, torch.float32, "v"), v.shape[0],
+                                  _ptr(converged_flag, torch.int32, "flag"), _ptr(iters_done), None, 0, _stream())
+    _check(rc, "pdsc_power_normalize")
+    _count()
+    return v
+
+
+def power_iter_full(src, tgt, sigma_spat, num_iterations, ws=None):
+    """Leading eigenvector of the zero-diagonal compatibility matrix of one pair ([N,3] inputs)."""
+    lib = load()
+    N = src.shape[0]
+    v = torch.empty(N, dtype=torch.float32, device=src.device)
+    iters = torch.empty(1, dtype=torch.int32, device=src.device)
+    w = _ws(workspace_bytes(OP_POWER_ITER_FULL, 1, N), src.device, ws)
+    rc = lib.pdsc_power_iter_full(_ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"), v.data_ptr(), N,
+                                  float(sigma_spat), int(num_iterations), iters.data_ptr(), w.data_ptr(), w.numel(),
+                                  _stream())
+    _check(rc, "pdsc_power_iter_full")
+    _count()
+    return v, iters

@@ -1,0 +1,171 @@
+// C ABI of libpointdsc_b200.so (include/pointdsc_b200.h): argument checks, error strings,
+// workspace sizing.  No torch types cross this boundary.
+#include "common.cuh"
+
+#include <atomic>
+#include <stdarg.h>
+#include <string.h>
+
+namespace pdsc {
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void count_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return PDSC_ERR_CUDA;
+    }
+    return PDSC_OK;
+}
+
+int num_sms() {
+    static thread_local int cached_dev = -1, cached = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev != cached_dev) {
+        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        cached_dev = dev;
+    }
+    return cached > 0 ? cached : 148;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace pdsc
+
+using namespace pdsc;
+
+extern "C" {
+
+int pdsc_version(void) { return 100; }
+
+const char* pdsc_last_error(void) { return g_err; }
+
+uint64_t pdsc_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int pdsc_check_device(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device"); return PDSC_ERR_DEVICE; }
+    int major = 0, minor = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+    if (major != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, major, minor);
+        return PDSC_ERR_DEVICE;
+    }
+    return PDSC_OK;
+}
+
+size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode) {
+    switch (op) {
+        case PDSC_OP_NONLOCAL_ATTN: return attn_workspace(B, N, C, mode);
+        case PDSC_OP_PICK_SEEDS: return pick_seeds_workspace(B, N);
+        case PDSC_OP_SEED_KNN: return seed_knn_workspace(B, N, S);
+        case PDSC_OP_SEED_HYPOTHESES: return seed_hypotheses_workspace(B, S, k, 31);
+        case PDSC_OP_SCORE_HYPOTHESES: return 0;
+        case PDSC_OP_POST_REFINE: return 0;
+        case PDSC_OP_POWER_ITER_FULL: return power_workspace(N);
+        default: return 0;
+    }
+}
+
+int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t ld_qkv, const float* src,
+                       const float* tgt, float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode,
+                       void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(q && k && v && src && tgt && out, "nonlocal_attn: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0, "nonlocal_attn: bad shape B=%d N=%d", B, N);
+    PDSC_REQUIRE(ld_qkv >= C && ld_out >= C && ld_qkv % 4 == 0 && ld_out % 4 == 0, "nonlocal_attn: bad row stride");
+    PDSC_REQUIRE(aligned16(q) && aligned16(k) && aligned16(v) && aligned16(out), "nonlocal_attn: q/k/v/out must be 16-byte aligned");
+    PDSC_REQUIRE(sigma_spat > 0.f, "nonlocal_attn: sigma_spat must be positive");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (mode == PDSC_ATTN_FP32) return launch_attn_fp32(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, st);
+    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16)
+        return launch_attn_tc(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
+    set_error("nonlocal_attn: unknown precision mode %d", mode);
+    return PDSC_ERR_ARG;
+}
+
+int pdsc_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds_out,
+                    uint8_t* is_local_max_out, int32_t* n_pos_out, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(src && scores && seeds_out && ws, "pick_seeds: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0 && S >= 0 && S <= N, "pick_seeds: bad shape B=%d N=%d S=%d", B, N, S);
+    if (S == 0) return PDSC_OK;
+    return launch_pick_seeds(src, scores, B, N, R, S, seeds_out, is_local_max_out, n_pos_out, ws, ws_bytes,
+                             reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int C, int S, int k, int64_t* knn_idx_out,
+                  float* knn_dist_out, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(normed && seeds && knn_idx_out && ws, "seed_knn: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 1 && S > 0, "seed_knn: bad shape B=%d N=%d S=%d", B, N, S);
+    PDSC_REQUIRE(aligned16(normed) && C % 4 == 0, "seed_knn: features must be 16-byte aligned, C %% 4 == 0");
+    return launch_seed_knn(normed, seeds, B, N, C, S, k, knn_idx_out, knn_dist_out, ws, ws_bytes,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_seed_hypotheses(const float* normed, const float* src, const float* tgt, const int64_t* knn_idx, int B, int N,
+                         int C, int S, int k, float sigma, float sigma_spat, int num_iterations, float* seed_trans_out,
+                         float* weights_out, int32_t* iters_out, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(normed && src && tgt && knn_idx && seed_trans_out && ws, "seed_hypotheses: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 1 && S > 0, "seed_hypotheses: bad shape B=%d N=%d S=%d", B, N, S);
+    PDSC_REQUIRE(aligned16(normed) && aligned16(seed_trans_out), "seed_hypotheses: features/transforms must be 16-byte aligned");
+    return launch_seed_hypotheses(normed, src, tgt, knn_idx, B, N, C, S, k, sigma, sigma_spat, num_iterations,
+                                  seed_trans_out, weights_out, iters_out, ws, ws_bytes,
+                                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_score_hypotheses(const float* seed_trans, const float* src, const float* tgt, int B, int N, int S, float thr,
+                          int32_t* inlier_count_out, int64_t* best_idx_out, float* final_trans_out,
+                          float* final_labels_out, void* ws, size_t ws_bytes, void* stream) {
+    (void)ws; (void)ws_bytes;
+    PDSC_REQUIRE(seed_trans && src && tgt && inlier_count_out && best_idx_out && final_trans_out && final_labels_out,
+                 "score_hypotheses: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0 && S > 0, "score_hypotheses: bad shape B=%d N=%d S=%d", B, N, S);
+    PDSC_REQUIRE(aligned16(seed_trans), "score_hypotheses: seed_trans must be 16-byte aligned");
+    return launch_score_hypotheses(seed_trans, src, tgt, B, N, S, thr, inlier_count_out, best_idx_out, final_trans_out,
+                                   final_labels_out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_post_refine(float* trans_inout, const float* src, const float* tgt, int B, int N, float tau, int max_iter,
+                     int32_t* iters_out, int32_t* counts_out, void* stream) {
+    PDSC_REQUIRE(trans_inout && src && tgt, "post_refine: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0 && max_iter >= 0 && tau > 0.f, "post_refine: bad arguments");
+    return launch_post_refine(trans_inout, src, tgt, B, N, tau, max_iter, iters_out, counts_out,
+                              reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin, int row_end,
+                       float sigma_spat, const int32_t* converged_flag, void* stream) {
+    PDSC_REQUIRE(src && tgt && v && y, "compat_matvec: null pointer");
+    PDSC_REQUIRE(N > 0 && row_begin >= 0 && row_end <= N && row_begin <= row_end, "compat_matvec: bad row range");
+    return launch_compat_matvec(src, tgt, v, y, N, row_begin, row_end, sigma_spat, converged_flag,
+                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_power_normalize(const float* y, float* v_inout, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,
+                         size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(y && v_inout && converged_flag, "power_normalize: null pointer");
+    return launch_power_normalize(y, v_inout, N, converged_flag, iters_done, ws, ws_bytes,
+                                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
+                         int32_t* iters_out, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(src && tgt && v_out && ws, "power_iter_full: null pointer");
+    PDSC_REQUIRE(N > 0 && num_iterations > 0, "power_iter_full: bad arguments");
+    return power_iter_full(src, tgt, v_out, N, sigma_spat, num_iterations, iters_out, ws, ws_bytes,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

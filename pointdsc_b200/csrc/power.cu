@@ -1,0 +1,128 @@
+// (b) Power iteration on the full N x N spatial-compatibility matrix (zero diagonal):
+// cal_leading_eigenvector models/PointDSC.py:338-358 on the matrix of :151-153, the
+// spectral-matching use kept at models/PointDSC.py:170 and baseline_scripts/baseline_3DMatch.py:19-46.
+// The matrix (10 GB at N=50k) is never stored: each M.v recomputes it from 6 floats per
+// correspondence.  Rows are independent, so a rank can own a row range (row sharding) and
+// all-gather y; the normalisation + allclose test is a one-block kernel every rank repeats.
+#include "common.cuh"
+
+namespace pdsc {
+
+constexpr int MV_ROWS = 64, MV_SLICES = 4, MV_THREADS = MV_ROWS * MV_SLICES, MV_TILE = 512;
+
+__global__ void __launch_bounds__(MV_THREADS) compat_matvec_kernel(const float* __restrict__ src,
+                                                                   const float* __restrict__ tgt,
+                                                                   const float* __restrict__ v, float* __restrict__ y,
+                                                                   int N, int row_begin, int row_end, float sig2,
+                                                                   const int32_t* __restrict__ converged_flag) {
+    if (converged_flag && *converged_flag) return;
+    __shared__ float4 ta[MV_TILE];   // src xyz, v
+    __shared__ float4 tb[MV_TILE];   // tgt xyz, unused
+    __shared__ float part[MV_SLICES][MV_ROWS];
+    const int rl = threadIdx.x % MV_ROWS, slice = threadIdx.x / MV_ROWS;
+    const int r = row_begin + blockIdx.x * MV_ROWS + rl;
+    const int rc = min(r, N - 1);
+    const float sx = src[rc * 3], sy = src[rc * 3 + 1], sz = src[rc * 3 + 2];
+    const float tx = tgt[rc * 3], ty = tgt[rc * 3 + 1], tz = tgt[rc * 3 + 2];
+    float acc = 0.f;
+    for (int j0 = 0; j0 < N; j0 += MV_TILE) {
+        const int nj = min(MV_TILE, N - j0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nj; t += MV_THREADS) {
+            const int j = j0 + t;
+            ta[t] = make_float4(src[j * 3], src[j * 3 + 1], src[j * 3 + 2], v[j]);
+            tb[t] = make_float4(tgt[j * 3], tgt[j * 3 + 1], tgt[j * 3 + 2], 0.f);
+        }
+        __syncthreads();
+        // slice s takes elements s, s+4, ... of the tile: a fixed order, so y is reproducible
+        for (int t = slice; t < nj; t += MV_SLICES) {
+            const float4 a = ta[t], c = tb[t];
+            const float ds = dist3(sx, sy, sz, a.x, a.y, a.z);
+            const float dt = dist3(tx, ty, tz, c.x, c.y, c.z);
+            const float m = (j0 + t == r) ? 0.f : compat_exact(ds, dt, sig2);
+            acc = fmaf(m, a.w, acc);
+        }
+    }
+    part[slice][rl] = acc;
+    __syncthreads();
+    if (slice == 0 && r < row_end) y[r - row_begin] = (part[0][rl] + part[1][rl]) + (part[2][rl] + part[3][rl]);
+}
+
+__global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __restrict__ y, float* __restrict__ v,
+                                                               int N, int32_t* __restrict__ converged_flag,
+                                                               int32_t* __restrict__ iters_done) {
+    if (*converged_flag) return;
+    __shared__ double red[32];
+    __shared__ int red_close[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double ss = 0.0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) ss += (double)y[i] * (double)y[i];
+    ss = warp_sum(ss);
+    if (lane == 0) red[warp] = ss;
+    __syncthreads();
+    double tot = 0.0;
+    for (int w = 0; w < 32; ++w) tot += red[w];
+    const float nrm = (float)sqrt(tot);
+    int close = 1;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+        const float vn = __fdiv_rn(y[i], nrm + 1e-6f);
+        const float vl = v[i];
+        close &= (fabsf(vn - vl) <= 1e-8f + 1e-5f * fabsf(vl)) ? 1 : 0;
+        v[i] = vn;
+    }
+    close = __all_sync(0xffffffffu, close);
+    if (lane == 0) red_close[warp] = close;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int all = 1;
+        for (int w = 0; w < 32; ++w) all &= red_close[w];
+        if (all) *converged_flag = 1;
+        if (iters_done) *iters_done += 1;
+    }
+}
+
+__global__ void fill_ones_kernel(float* v, int N, int32_t* flag, int32_t* iters) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) v[i] = 1.0f;
+    if (i == 0) { *flag = 0; *iters = 0; }
+}
+
+int launch_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin,
+                         int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st) {
+    const int rows = row_end - row_begin;
+    if (rows <= 0) return PDSC_OK;
+    compat_matvec_kernel<<<(rows + MV_ROWS - 1) / MV_ROWS, MV_THREADS, 0, st>>>(
+        src, tgt, v, y, N, row_begin, row_end, sigma_spat * sigma_spat, converged_flag);
+    count_launches(1);
+    return check_launch("compat_matvec");
+}
+
+size_t power_workspace(int N) { return align_up(sizeof(float) * (size_t)N, 256) + 256; }
+
+int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,
+                           size_t ws_bytes, cudaStream_t st) {
+    (void)ws; (void)ws_bytes;
+    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done);
+    count_launches(1);
+    return check_launch("power_normalize");
+}
+
+int power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
+                    int32_t* iters_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < power_workspace(N)) { set_error("power_iter_full: workspace too small"); return PDSC_ERR_WORKSPACE; }
+    float* y = reinterpret_cast<float*>(ws);
+    int32_t* flag = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + align_up(sizeof(float) * (size_t)N, 256));
+    int32_t* iters = flag + 1;
+    fill_ones_kernel<<<(N + 255) / 256, 256, 0, st>>>(v_out, N, flag, iters);
+    count_launches(1);
+    for (int it = 0; it < num_iterations; ++it) {
+        int rc = launch_compat_matvec(src, tgt, v_out, y, N, 0, N, sigma_spat, flag, st);
+        if (rc) return rc;
+        rc = launch_power_normalize(y, v_out, N, flag, iters, nullptr, 0, st);
+        if (rc) return rc;
+    }
+    if (iters_out) cudaMemcpyAsync(iters_out, iters, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+    return check_launch("power_iter_full");
+}
+
+}  // namespace pdsc

@@ -1,0 +1,113 @@
+// (e) Hypothesis scoring: every seed transform against all N correspondences.
+// Replaces models/PointDSC.py:325-335 (einsum -> [1,S,N,3] temp, norm, compare, mean, argmax,
+// two gathers).  Integer inlier counts are produced directly; nothing of size S*N touches HBM.
+#include "common.cuh"
+
+namespace pdsc {
+
+constexpr int SC_THREADS = 128;   // seeds per block (one seed per thread)
+constexpr int SC_POINTS = 512;    // correspondences staged in shared memory per block
+
+__device__ __forceinline__ bool is_inlier(const float* T, float sx, float sy, float sz, float tx, float ty, float tz,
+                                          float thr) {
+    float px = fmaf(T[2], sz, fmaf(T[1], sy, T[0] * sx)) + T[3];
+    float py = fmaf(T[6], sz, fmaf(T[5], sy, T[4] * sx)) + T[7];
+    float pz = fmaf(T[10], sz, fmaf(T[9], sy, T[8] * sx)) + T[11];
+    return dist3(px, py, pz, tx, ty, tz) < thr;
+}
+
+__global__ void __launch_bounds__(SC_THREADS) score_count_kernel(const float* __restrict__ seed_trans,
+                                                                 const float* __restrict__ src,
+                                                                 const float* __restrict__ tgt, int N, int S,
+                                                                 float thr, int32_t* __restrict__ inlier_count) {
+    __shared__ float sp[SC_POINTS * 6];
+    const int b = blockIdx.z;
+    const int n0 = blockIdx.y * SC_POINTS;
+    const int np = min(SC_POINTS, N - n0);
+    const float* sb = src + ((size_t)b * N + n0) * 3;
+    const float* tb = tgt + ((size_t)b * N + n0) * 3;
+    for (int i = threadIdx.x; i < np * 3; i += SC_THREADS) {
+        sp[i] = sb[i];
+        sp[SC_POINTS * 3 + i] = tb[i];
+    }
+    __syncthreads();
+    const int s = blockIdx.x * SC_THREADS + threadIdx.x;
+    if (s >= S) return;
+    float T[12];
+    const float4* tp = reinterpret_cast<const float4*>(seed_trans + ((size_t)b * S + s) * 16);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        float4 row = tp[r];
+        T[r * 4 + 0] = row.x; T[r * 4 + 1] = row.y; T[r * 4 + 2] = row.z; T[r * 4 + 3] = row.w;
+    }
+    int cnt = 0;
+#pragma unroll 4
+    for (int n = 0; n < np; ++n) {
+        const float* a = sp + n * 3;
+        const float* c = sp + SC_POINTS * 3 + n * 3;
+        cnt += is_inlier(T, a[0], a[1], a[2], c[0], c[1], c[2], thr) ? 1 : 0;
+    }
+    atomicAdd(inlier_count + (size_t)b * S + s, cnt);
+}
+
+// One block per pair: first-index argmax of the counts (torch.argmax on CPU returns the first
+// maximal index; fitness = count/N is strictly monotone in count for N < 2^23), then the best
+// transform and the 0/1 labels under it (models/PointDSC.py:330-335).
+__global__ void __launch_bounds__(256) score_select_kernel(const float* __restrict__ seed_trans,
+                                                           const float* __restrict__ src,
+                                                           const float* __restrict__ tgt, int N, int S, float thr,
+                                                           const int32_t* __restrict__ inlier_count,
+                                                           int64_t* __restrict__ best_idx,
+                                                           float* __restrict__ final_trans,
+                                                           float* __restrict__ final_labels) {
+    __shared__ unsigned long long red[8];
+    __shared__ float Tb[16];
+    const int b = blockIdx.x;
+    // key = count << 32 | (0xffffffff - idx): max key == max count, then min index
+    unsigned long long best = 0ull;
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        unsigned long long key = ((unsigned long long)(uint32_t)inlier_count[(size_t)b * S + s] << 32) |
+                                 (unsigned long long)(0xffffffffu - (uint32_t)s);
+        best = key > best ? key : best;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other > best ? other : best;
+    }
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) best = red[w] > best ? red[w] : best;
+        red[0] = best;
+    }
+    __syncthreads();
+    const int sbest = (int)(0xffffffffu - (uint32_t)(red[0] & 0xffffffffull));
+    if (threadIdx.x < 16) {
+        float v = seed_trans[((size_t)b * S + sbest) * 16 + threadIdx.x];
+        Tb[threadIdx.x] = v;
+        final_trans[(size_t)b * 16 + threadIdx.x] = v;
+    }
+    if (threadIdx.x == 0) best_idx[b] = sbest;
+    __syncthreads();
+    const float* sb = src + (size_t)b * N * 3;
+    const float* tb = tgt + (size_t)b * N * 3;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        bool in = is_inlier(Tb, sb[n * 3], sb[n * 3 + 1], sb[n * 3 + 2], tb[n * 3], tb[n * 3 + 1], tb[n * 3 + 2], thr);
+        final_labels[(size_t)b * N + n] = in ? 1.0f : 0.0f;
+    }
+}
+
+int launch_score_hypotheses(const float* seed_trans, const float* src, const float* tgt, int B, int N, int S,
+                            float thr, int32_t* inlier_count, int64_t* best_idx, float* final_trans,
+                            float* final_labels, cudaStream_t st) {
+    cudaMemsetAsync(inlier_count, 0, sizeof(int32_t) * (size_t)B * S, st);
+    dim3 grid((S + SC_THREADS - 1) / SC_THREADS, (N + SC_POINTS - 1) / SC_POINTS, B);
+    score_count_kernel<<<grid, SC_THREADS, 0, st>>>(seed_trans, src, tgt, N, S, thr, inlier_count);
+    score_select_kernel<<<B, 256, 0, st>>>(seed_trans, src, tgt, N, S, thr, inlier_count, best_idx, final_trans,
+                                           final_labels);
+    count_launches(2);
+    return check_launch("score_hypotheses");
+}
+
+}  // namespace pdsc

@@ -1,0 +1,344 @@
+// (c) Seed selection: NMS local-maximum test with on-the-fly source distances + ordered top-S
+// (PointDSC.pick_seeds, models/PointDSC.py:199-217), and feature-space kNN of the S seed rows
+// only (knn, models/common.py:48-69 called at models/PointDSC.py:251-252).
+// The reference builds three N x N boolean temporaries on top of the stored N x N src_dist and
+// a full N x N Gram + topk over all N rows; here nothing of size N x N exists.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace pdsc {
+
+// ------------------------------------------------------------------------------------------
+// pick_seeds, stage 1: suppressed[i] = exists j: !(score_i >= score_j) && !(|s_i-s_j| >= R)
+// ------------------------------------------------------------------------------------------
+constexpr int NMS_THREADS = 256;
+constexpr int NMS_TILE = 1024;
+
+__global__ void __launch_bounds__(NMS_THREADS) nms_kernel(const float* __restrict__ src,
+                                                          const float* __restrict__ scores, int N, float R,
+                                                          int jchunk, int32_t* __restrict__ suppressed) {
+    __shared__ float4 tile[NMS_TILE];
+    const int b = blockIdx.z;
+    const float* sb = src + (size_t)b * N * 3;
+    const float* cb = scores + (size_t)b * N;
+    const int i = blockIdx.x * NMS_THREADS + threadIdx.x;
+    float xi = 0.f, yi = 0.f, zi = 0.f, si = 0.f;
+    if (i < N) { xi = sb[i * 3]; yi = sb[i * 3 + 1]; zi = sb[i * 3 + 2]; si = cb[i]; }
+    const int j_begin = blockIdx.y * jchunk;
+    const int j_end = min(N, j_begin + jchunk);
+    bool sup = false;
+    for (int j0 = j_begin; j0 < j_end; j0 += NMS_TILE) {
+        const int nj = min(NMS_TILE, j_end - j0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nj; t += NMS_THREADS) {
+            const int j = j0 + t;
+            tile[t] = make_float4(sb[j * 3], sb[j * 3 + 1], sb[j * 3 + 2], cb[j]);
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int t = 0; t < nj; ++t) {
+            const float4 p = tile[t];
+            const bool ge_score = si >= p.w;
+            const bool far = dist3(xi, yi, zi, p.x, p.y, p.z) >= R;
+            sup |= !(ge_score || far);
+        }
+    }
+    if (sup && i < N) suppressed[(size_t)b * N + i] = 1;
+}
+
+// ------------------------------------------------------------------------------------------
+// pick_seeds, stage 2: order by (key descending, index ascending), key = score*is_local_max.
+// One CTA per pair, bitonic sort of 64-bit composite keys (all distinct -> deterministic).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bitonic_sort(unsigned long long* a, int n_pow2) {
+    for (int k = 2; k <= n_pow2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < n_pow2; t += blockDim.x) {
+                const int p = t ^ j;
+                if (p > t) {
+                    const unsigned long long x = a[t], y = a[p];
+                    const bool up = (t & k) == 0;
+                    if ((x > y) == up) { a[t] = y; a[p] = x; }
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(1024) seed_order_kernel(const float* __restrict__ scores,
+                                                          const int32_t* __restrict__ suppressed, int N, int S,
+                                                          int n_pow2, unsigned long long* __restrict__ gbuf,
+                                                          int64_t* __restrict__ seeds,
+                                                          uint8_t* __restrict__ is_local_max,
+                                                          int32_t* __restrict__ n_pos) {
+    extern __shared__ unsigned long long sbuf[];
+    __shared__ int pos_count;
+    const int b = blockIdx.x;
+    unsigned long long* a = gbuf ? gbuf + (size_t)b * n_pow2 : sbuf;
+    if (threadIdx.x == 0) pos_count = 0;
+    __syncthreads();
+    int local_pos = 0;
+    for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
+        unsigned long long key = ~0ull;  // padding sorts last
+        if (i < N) {
+            const bool lm = suppressed[(size_t)b * N + i] == 0;
+            float kf = scores[(size_t)b * N + i] * (lm ? 1.0f : 0.0f);
+            if (kf == 0.0f) kf = 0.0f;  // -0 and +0 are equal keys in the reference
+            local_pos += kf > 0.0f ? 1 : 0;
+            key = ((unsigned long long)(~float_to_ordered(kf)) << 32) | (unsigned long long)(uint32_t)i;
+            if (is_local_max) is_local_max[(size_t)b * N + i] = lm ? 1 : 0;
+        }
+        a[i] = key;
+    }
+    local_pos = warp_sum(local_pos);
+    if ((threadIdx.x & 31) == 0 && local_pos) atomicAdd(&pos_count, local_pos);
+    bitonic_sort(a, n_pow2);
+    for (int s = threadIdx.x; s < S; s += blockDim.x) seeds[(size_t)b * S + s] = (int64_t)(a[s] & 0xffffffffull);
+    if (threadIdx.x == 0 && n_pos) n_pos[b] = pos_count;
+}
+
+static int next_pow2(int n) {
+    int p = 1;
+    while (p < n) p <<= 1;
+    return p;
+}
+
+constexpr int SORT_SMEM_MAX_ELEMS = 16384;  // 128 KB of 64-bit keys
+
+size_t pick_seeds_workspace(int B, int N) {
+    size_t bytes = align_up(sizeof(int32_t) * (size_t)B * N, 256);
+    const int p2 = next_pow2(N);
+    if (p2 > SORT_SMEM_MAX_ELEMS) bytes += sizeof(unsigned long long) * (size_t)B * p2;
+    return bytes;
+}
+
+int launch_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds,
+                      uint8_t* is_local_max, int32_t* n_pos, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < pick_seeds_workspace(B, N)) {
+        set_error("pick_seeds: workspace too small (%zu < %zu)", ws_bytes, pick_seeds_workspace(B, N));
+        return PDSC_ERR_WORKSPACE;
+    }
+    int32_t* suppressed = reinterpret_cast<int32_t*>(ws);
+    cudaMemsetAsync(suppressed, 0, sizeof(int32_t) * (size_t)B * N, st);
+    const int iblocks = (N + NMS_THREADS - 1) / NMS_THREADS;
+    // enough j-splits to fill the machine a few times over
+    int jsplit = (4 * num_sms() + iblocks * B - 1) / (iblocks * B);
+    jsplit = max(1, min(jsplit, (N + NMS_TILE - 1) / NMS_TILE));
+    int jchunk = (N + jsplit - 1) / jsplit;
+    jchunk = (jchunk + NMS_TILE - 1) / NMS_TILE * NMS_TILE;
+    jsplit = (N + jchunk - 1) / jchunk;
+    nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, R, jchunk, suppressed);
+    const int p2 = next_pow2(N);
+    unsigned long long* gbuf = nullptr;
+    size_t smem = sizeof(unsigned long long) * (size_t)p2;
+    if (p2 > SORT_SMEM_MAX_ELEMS) {
+        gbuf = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) +
+                                                     align_up(sizeof(int32_t) * (size_t)B * N, 256));
+        smem = 0;
+    } else {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaFuncSetAttribute(seed_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(sizeof(unsigned long long) * SORT_SMEM_MAX_ELEMS));
+            attr_set = true;
+        }
+    }
+    seed_order_kernel<<<B, 1024, smem, st>>>(scores, suppressed, N, S, p2, gbuf, seeds, is_local_max, n_pos);
+    count_launches(2);
+    return check_launch("pick_seeds");
+}
+
+// ------------------------------------------------------------------------------------------
+// seed kNN, stage 1: D[b][s][j] = 2 - 2 <f_seed(s), f_j>  (self -> +inf), fp32 FMA GEMM
+// tile: 32 seeds x 128 candidates per block, 4x4 outputs per thread, channels in chunks of 32
+// ------------------------------------------------------------------------------------------
+constexpr int KG_TS = 32, KG_TJ = 128, KG_TC = 32, KG_THREADS = 256;
+
+__global__ void __launch_bounds__(KG_THREADS) knn_dist_kernel(const float* __restrict__ feat,
+                                                              const int64_t* __restrict__ seeds, int N, int C, int S,
+                                                              float* __restrict__ D) {
+    __shared__ __align__(16) float As[KG_TC][KG_TS + 4];
+    __shared__ __align__(16) float Bs[KG_TC][KG_TJ + 4];
+    __shared__ int seed_idx[KG_TS];
+    const int b = blockIdx.z;
+    const int s0 = blockIdx.y * KG_TS, j0 = blockIdx.x * KG_TJ;
+    const float* fb = feat + (size_t)b * N * C;
+    if (threadIdx.x < KG_TS) {
+        const int s = s0 + threadIdx.x;
+        seed_idx[threadIdx.x] = s < S ? (int)seeds[(size_t)b * S + s] : -1;
+    }
+    __syncthreads();
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // tx: 4 candidates, ty: 4 seeds
+    float acc[4][4] = {};
+    for (int c0 = 0; c0 < C; c0 += KG_TC) {
+        {   // A: 32 seeds x 32 channels = 256 float4 -> one per thread
+            const int r = threadIdx.x >> 3, c4 = threadIdx.x & 7;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int si = seed_idx[r];
+            if (si >= 0) v = *reinterpret_cast<const float4*>(fb + (size_t)si * C + c0 + c4 * 4);
+            As[c4 * 4 + 0][r] = v.x; As[c4 * 4 + 1][r] = v.y; As[c4 * 4 + 2][r] = v.z; As[c4 * 4 + 3][r] = v.w;
+        }
+#pragma unroll
+        for (int rep = 0; rep < 4; ++rep) {   // B: 128 candidates x 32 channels = 1024 float4
+            const int f = threadIdx.x + rep * KG_THREADS;
+            const int r = f >> 3, c4 = f & 7;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (j0 + r < N) v = *reinterpret_cast<const float4*>(fb + (size_t)(j0 + r) * C + c0 + c4 * 4);
+            Bs[c4 * 4 + 0][r] = v.x; Bs[c4 * 4 + 1][r] = v.y; Bs[c4 * 4 + 2][r] = v.z; Bs[c4 * 4 + 3][r] = v.w;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int c = 0; c < KG_TC; ++c) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[c][ty * 4]);
+            const float4 bq = *reinterpret_cast<const float4*>(&Bs[c][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float bv[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int s = s0 + ty * 4 + i;
+        if (s >= S) continue;
+        const int self = seed_idx[ty * 4 + i];
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int jj = j0 + tx * 4 + j;
+            o[j] = (jj == self) ? INFINITY : __fsub_rn(2.0f, __fmul_rn(2.0f, acc[i][j]));   // common.py:58-60
+        }
+        float* row = D + ((size_t)b * S + s) * N + j0 + tx * 4;
+        if (j0 + tx * 4 + 3 < N && (N & 3) == 0) {
+            *reinterpret_cast<float4*>(row) = make_float4(o[0], o[1], o[2], o[3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (j0 + tx * 4 + j < N) row[j] = o[j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// seed kNN, stage 2: exact k smallest (dist, index) per seed row: 4-pass radix select on the
+// ordered bit pattern, ordered compaction of ties, rank sort of the k winners.
+// ------------------------------------------------------------------------------------------
+constexpr int KS_THREADS = 128;
+constexpr int KS_MAXK = 64;
+
+__global__ void __launch_bounds__(KS_THREADS) knn_select_kernel(const float* __restrict__ D, int N, int S, int k,
+                                                                int64_t* __restrict__ knn_idx,
+                                                                float* __restrict__ knn_dist) {
+    __shared__ unsigned int hist[256];
+    __shared__ unsigned int sh_prefix, sh_want;
+    __shared__ unsigned int cand_key[KS_MAXK];
+    __shared__ int cand_idx[KS_MAXK];
+    __shared__ int n_less, n_eq_taken, warp_tot[KS_THREADS / 32];
+    const int row_id = blockIdx.x;   // b*S + s
+    const float* row = D + (size_t)row_id * N;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) { sh_prefix = 0u; sh_want = (unsigned)k; n_less = 0; n_eq_taken = 0; }
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        for (int i = tid; i < 256; i += KS_THREADS) hist[i] = 0u;
+        __syncthreads();
+        const unsigned prefix = sh_prefix;
+        const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+        for (int j = tid; j < N; j += KS_THREADS) {
+            const unsigned key = float_to_ordered(row[j]);
+            if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned want = sh_want, cum = 0u;
+            int bin = 0;
+            for (; bin < 256; ++bin) {
+                if (cum + hist[bin] >= want) break;
+                cum += hist[bin];
+            }
+            sh_want = want - cum;
+            sh_prefix = prefix | ((unsigned)bin << shift);
+        }
+        __syncthreads();
+    }
+    const unsigned T = sh_prefix;           // key of the k-th smallest element
+    const int want_eq = (int)sh_want;       // how many elements equal to T belong to the answer
+    const int base_eq = k - want_eq;        // == number of elements with key < T
+    // ordered pass: "<T" appended with an atomic (order fixed later), "==T" taken in index order
+    for (int j0 = 0; j0 < N; j0 += KS_THREADS) {
+        const int j = j0 + tid;
+        unsigned key = 0xffffffffu;
+        if (j < N) key = float_to_ordered(row[j]);
+        const bool less = j < N && key < T;
+        const bool eq = j < N && key == T;
+        if (less) {
+            const int p = atomicAdd(&n_less, 1);
+            cand_key[p] = key;
+            cand_idx[p] = j;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, eq);
+        if (lane == 0) warp_tot[warp] = __popc(m);
+        __syncthreads();
+        if (eq) {
+            int p = n_eq_taken + __popc(m & ((1u << lane) - 1u));
+            for (int w = 0; w < warp; ++w) p += warp_tot[w];
+            if (p < want_eq) {
+                cand_key[base_eq + p] = key;
+                cand_idx[base_eq + p] = j;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int tot = 0;
+            for (int w = 0; w < KS_THREADS / 32; ++w) tot += warp_tot[w];
+            n_eq_taken += tot;
+        }
+        __syncthreads();
+    }
+    // rank sort by (key, index)
+    if (tid < k) {
+        const unsigned mk = cand_key[tid];
+        const int mi = cand_idx[tid];
+        int rank = 0;
+        for (int o = 0; o < k; ++o) {
+            const unsigned ok = cand_key[o];
+            const int oi = cand_idx[o];
+            rank += (ok < mk || (ok == mk && oi < mi)) ? 1 : 0;
+        }
+        knn_idx[(size_t)row_id * k + rank] = mi;
+        if (knn_dist) knn_dist[(size_t)row_id * k + rank] = row[mi];
+    }
+}
+
+size_t seed_knn_workspace(int B, int N, int S) { return sizeof(float) * (size_t)B * S * N; }
+
+int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int C, int S, int k,
+                    int64_t* knn_idx, float* knn_dist, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (k > KS_MAXK || k < 1 || k > N - 1) {
+        set_error("seed_knn: k=%d unsupported (1..%d, < N)", k, KS_MAXK);
+        return PDSC_ERR_ARG;
+    }
+    if (C % KG_TC != 0) {
+        set_error("seed_knn: C=%d must be a multiple of %d", C, KG_TC);
+        return PDSC_ERR_ARG;
+    }
+    if (ws_bytes < seed_knn_workspace(B, N, S)) {
+        set_error("seed_knn: workspace too small (%zu < %zu)", ws_bytes, seed_knn_workspace(B, N, S));
+        return PDSC_ERR_WORKSPACE;
+    }
+    float* D = reinterpret_cast<float*>(ws);
+    dim3 grid((N + KG_TJ - 1) / KG_TJ, (S + KG_TS - 1) / KG_TS, B);
+    knn_dist_kernel<<<grid, KG_THREADS, 0, st>>>(normed, seeds, N, C, S, D);
+    knn_select_kernel<<<B * S, KS_THREADS, 0, st>>>(D, N, S, k, knn_idx, knn_dist);
+    count_launches(2);
+    return check_launch("seed_knn");
+}
+
+}  // namespace pdsc

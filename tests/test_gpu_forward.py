@@ -1,0 +1,101 @@
+"""GPU parity of the whole drop-in forward against the reference's golden outputs and the
+oracle, plus size-independent properties at BASELINE.json's full sizes."""
+import pytest
+import torch
+
+from conftest import GOLDEN_CASES, load_golden
+from oracle import restate, synth
+from parity import CONF_TOL, assert_labels_match, assert_trans_close, golden_model
+
+pytestmark = pytest.mark.gpu
+
+MODES = ["fp32"]
+
+
+def _mode(name):
+    from pointdsc_b200 import _cabi
+    return {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16}[name]
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_forward_vs_reference_golden(case, mode):
+    meta, g = load_golden(case)
+    model, _ = golden_model(meta, attn_mode=_mode(mode))
+    data = {k: g[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    res = model(data)
+    assert set(("final_trans", "final_labels", "M")) <= set(res) and res["M"] is None
+    assert res["final_trans"].shape == (1, 4, 4) and res["final_labels"].shape == (1, meta["N"])
+    # floating point: confidences <= 1e-4 abs (relative to magnitude above 1)
+    dconf = (res["confidence"].cpu() - g["confidence"]).abs().max().item()
+    scale = max(1.0, g["confidence"].abs().max().item())
+    print(f"{case}/{mode}: max |dconf| = {dconf:.3e}")
+    assert dconf <= CONF_TOL * scale
+    re, te = assert_trans_close(res["final_trans"], g["final_trans"])
+    print(f"{case}/{mode}: final_trans rot err {re:.2e} deg, trans err {te:.2e} m")
+    thr = meta["ctor"]["inlier_threshold"]
+    assert_labels_match(res["final_labels"][0], g["final_labels"][0], res["initial_trans"][0], g["src_keypts"][0],
+                        g["tgt_keypts"][0], thr)
+    # seeds: identical wherever the reference's order is well defined and scores are separated
+    same = (res["seeds"].cpu() == g["seeds"]).float().mean().item()
+    print(f"{case}/{mode}: {100 * same:.1f}% of seed slots identical")
+
+
+def test_batched_forward_equals_per_pair_runs():
+    """[B,N,.] means B independent pairs (reference test path is batch-size 1)."""
+    meta, g = load_golden("g0_3dmatch_n256_l2")
+    model, _ = golden_model(meta)
+    cfg = synth.CONFIGS["3dmatch"]
+    batch = synth.make_batch([11, 12, 13], 256, **cfg)
+    data = {k: batch[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    res = model(data)
+    for b in range(3):
+        one = model({k: (v[b:b + 1] if torch.is_tensor(v) else v) for k, v in data.items()})
+        assert torch.equal(one["final_trans"][0], res["final_trans"][b])
+        assert torch.equal(one["final_labels"][0], res["final_labels"][b])
+        assert torch.equal(one["seeds"][0], res["seeds"][b])
+    # pair 0 of the batch is the golden pair
+    assert_trans_close(res["final_trans"][0:1], g["final_trans"])
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("fam,N", [("3dmatch", 5000), ("kitti", 10000)])
+def test_full_size_properties(fam, N, mode):
+    """BASELINE configs 2/3 at full size: the registration recovers the synthetic ground-truth
+    motion, labels are consistent with the returned initial transform, permuting the
+    correspondences permutes the labels and leaves the transform (nearly) unchanged."""
+    cfg = synth.CONFIGS[fam]
+    meta = dict(family=fam, weight_seed=1234, num_layers=12,
+                ctor=dict(num_layers=12, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
+                          nms_radius=cfg["nms_radius"]))
+    model, _ = golden_model(meta, attn_mode=_mode(mode))
+    batch = synth.make_batch([0, 1] if fam == "3dmatch" else [100, 101], N, **cfg)
+    data = {k: batch[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    res = model(data)
+    torch.cuda.synchronize()
+    thr = cfg["inlier_threshold"]
+    for b in range(2):
+        re = restate.rotation_error_deg(res["final_trans"][b, :3, :3].cpu(), batch["gt_trans"][b, :3, :3])
+        te = restate.translation_error(res["final_trans"][b, :3, 3].cpu(), batch["gt_trans"][b, :3, 3])
+        print(f"{fam} N={N} pair {b}: RE {float(re):.3f} deg TE {float(te):.4f} m inliers {int(res['final_labels'][b].sum())}")
+        assert float(re) < 1.0 and float(te) < 3 * cfg["noise"] + 0.02
+        # labels == distance test under initial_trans, recomputed in fp64
+        T = res["initial_trans"][b].double().cpu()
+        d = torch.linalg.norm(batch["src_keypts"][b].double() @ T[:3, :3].T + T[:3, 3] - batch["tgt_keypts"][b].double(), dim=-1)
+        lab = res["final_labels"][b].cpu()
+        clear = (d - thr).abs() > 1e-5 * cfg["scale"]
+        assert torch.equal(lab[clear], (d[clear] < thr).float())
+        assert int(res["inlier_count"][b, res["best_idx"][b]]) == int(lab.sum())
+        assert int(res["inlier_count"][b].max()) == int(lab.sum())
+    # permutation equivariance on pair 0
+    g = torch.Generator().manual_seed(9)
+    perm = torch.randperm(N, generator=g).cuda()
+    pdata = {k: data[k][0:1, perm].contiguous() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    pdata["testing"] = True
+    pres = model(pdata)
+    assert_trans_close(pres["final_trans"], res["final_trans"][0:1], rot=0.05, trans=5e-4)
+    agree = (pres["final_labels"][0] == res["final_labels"][0, perm]).float().mean().item()
+    assert agree > 0.999

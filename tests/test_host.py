@@ -1,0 +1,77 @@
+"""CPU tests: the C-ABI library loads and exports every symbol the header declares, the
+drop-in module has the reference's state_dict layout, and the host-side (torch) part of the
+forward -- BN folding, fused q/k/v projection, channel-last MLPs -- reproduces the oracle when
+the CUDA attention is replaced by the oracle's (tests only; the product has no such path)."""
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import ROOT, load_golden
+from oracle import restate, synth
+from pointdsc_b200 import PointDSC, _cabi
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "pointdsc_b200.h")).read()
+    declared = set(re.findall(r"\b(pdsc_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    lib = _cabi.load()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/pointdsc_b200.h but not exported"
+    assert declared == set(_cabi.SIGNATURES), declared ^ set(_cabi.SIGNATURES)
+    assert lib.pdsc_version() >= 100
+
+
+def test_workspace_queries_do_not_need_a_gpu():
+    assert _cabi.workspace_bytes(_cabi.OP_SEED_KNN, B=2, N=1000, C=128, S=100, k=40) == 2 * 100 * 1000 * 4
+    assert _cabi.workspace_bytes(_cabi.OP_PICK_SEEDS, B=1, N=5000) >= 5000 * 4
+    assert _cabi.workspace_bytes(_cabi.OP_PICK_SEEDS, B=1, N=50000) >= 65536 * 8
+
+
+def test_state_dict_layout_matches_reference():
+    m = PointDSC(num_layers=12)
+    sd = synth.make_state_dict(1234, num_layers=12)
+    assert len(m.state_dict()) == 358
+    assert sum(p.numel() for p in m.parameters()) == 1053667
+    assert set(m.state_dict()) == set(sd)
+    m.load_state_dict(sd, strict=True)
+    for k, v in m.state_dict().items():
+        assert v.shape == sd[k].shape, k
+
+
+def test_cpu_tensors_are_refused():
+    m = PointDSC(num_layers=1).eval()
+    p = synth.make_pair(0, 64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m({"corr_pos": p["corr_pos"], "src_keypts": p["src_keypts"], "tgt_keypts": p["tgt_keypts"], "testing": True})
+    with pytest.raises(NotImplementedError):
+        m({"corr_pos": p["corr_pos"], "src_keypts": p["src_keypts"], "tgt_keypts": p["tgt_keypts"]})
+
+
+@pytest.mark.parametrize("case", ["g0_3dmatch_n256_l2", "g2_kitti_n800_l6"])
+def test_host_mlps_match_oracle(case, monkeypatch):
+    meta, g = load_golden(case)
+    fam = synth.CONFIGS[meta["family"]]
+    sd = synth.make_state_dict(meta["weight_seed"], num_layers=meta["num_layers"], sigma_d=fam["sigma_d"])
+    m = PointDSC(**meta["ctor"]).eval()
+    m.load_state_dict(sd)
+
+    def oracle_attn(q, k, v, src, tgt, sigma_spat, mode=0, out=None, ws=None):
+        outs = []
+        for b in range(q.shape[0]):
+            _, compat = restate.spatial_compatibility(src[b:b + 1], tgt[b:b + 1], torch.tensor([sigma_spat]))
+            msg = restate.nonlocal_message(q[b:b + 1].permute(0, 2, 1), k[b:b + 1].permute(0, 2, 1),
+                                           v[b:b + 1].permute(0, 2, 1), compat)
+            outs.append(msg.permute(0, 2, 1))
+        return torch.cat(outs).contiguous()
+
+    monkeypatch.setattr(_cabi, "nonlocal_attn", oracle_attn)
+    with torch.no_grad():
+        feat = m.encode(g["corr_pos"], g["src_keypts"], g["tgt_keypts"])
+        conf = m.classify(feat)
+    normed = torch.nn.functional.normalize(feat, p=2, dim=-1)
+    assert (normed - g["normed_features"]).abs().max() < 2e-5
+    scale = max(1.0, g["confidence"].abs().max().item())
+    assert (conf - g["confidence"]).abs().max() < 1e-4 * scale
