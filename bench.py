@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""Throughput benchmark of the PointDSC hot path (BASELINE.json: registration pairs/sec).
+
+A "step" is one pass of the hot path -- PointDSC.forward(data) in test mode -- over one batch
+of synthetic registration pairs (default: BASELINE configs[1], 16 pairs x N=5000 correspondences,
+10% inliers, 3DMatch hyper-parameters, 12 layers, seeded weights).  With --gpus N every rank
+(one process per GPU, launched by torch.distributed.run) processes its own batch: the path
+shards by pair with no communication (weak scaling), value = all pairs / max-over-ranks time.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+`--impl reference` times the reference's CPU implementation of the same path (the oracle port of
+models/PointDSC.py, all host threads) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "registration_pairs_per_sec"
+UNIT = "pairs/s"
+NUM_LAYERS = 12
+C = 128
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=16, help="pairs per step per GPU")
+    ap.add_argument("--n", type=int, default=5000, help="correspondences per pair")
+    ap.add_argument("--family", default="3dmatch", choices=["3dmatch", "kitti"])
+    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "fp32"), choices=["fp32", "split16", "fp16"])
+    ap.add_argument("--cpu-pairs", type=int, default=3, help="pairs in the cpu_baseline sample (first is warm-up)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(args):
+    return f"synthetic {args.family}-shaped: {args.pairs} pairs x N={args.n} correspondences per GPU, " \
+           f"{NUM_LAYERS} layers, C={C}, seeded weights"
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(hbm=p["hbm_gbs"], bf16_burst=p["bf16_tflops"], bf16_sustained=p["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake_slowdown",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+def make_inputs(args, rank):
+    from oracle import synth   # seeded generator only (no oracle arithmetic on the product path)
+    cfg = synth.CONFIGS[args.family]
+    base = 0 if args.family == "3dmatch" else 100
+    seeds = [base + rank * args.pairs + i for i in range(args.pairs)]
+    batch = synth.make_batch(seeds, args.n, **cfg)
+    sd = synth.make_state_dict(1234, num_layers=NUM_LAYERS, sigma_d=cfg["sigma_d"])
+    return cfg, batch, sd
+
+
+def cpu_baseline(args, cfg, batch, sd, n_pairs):
+    """The oracle port of the reference forward, all host threads, one pair at a time."""
+    from oracle import restate
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    times = []
+    for i in range(n_pairs):
+        t0 = time.perf_counter()
+        restate.forward_pair(sd, batch["corr_pos"][i:i + 1], batch["src_keypts"][i:i + 1], batch["tgt_keypts"][i:i + 1],
+                             num_layers=NUM_LAYERS, inlier_threshold=cfg["inlier_threshold"],
+                             nms_radius=cfg["nms_radius"])
+        times.append(time.perf_counter() - t0)
+    timed = times[1:] if len(times) > 1 else times
+    mean = sum(timed) / len(timed)
+    return dict(value=1.0 / mean, unit=UNIT, cores=cores, kind="port",
+                sample=f"{len(timed)} pair(s) of the same workload (N={args.n}) after 1 warm-up pair, "
+                       f"oracle/restate.py (port of models/PointDSC.py forward), torch CPU fp32, {cores} threads",
+                s_per_pair=mean)
+
+
+def run_reference(args):
+    """--impl reference: CPU implementation of the path on the host cores; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg, batch, sd = make_inputs(args, 0)
+    from oracle import restate
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+
+    def one(i):
+        i = i % args.pairs
+        restate.forward_pair(sd, batch["corr_pos"][i:i + 1], batch["src_keypts"][i:i + 1], batch["tgt_keypts"][i:i + 1],
+                             num_layers=NUM_LAYERS, inlier_threshold=cfg["inlier_threshold"], nms_radius=cfg["nms_radius"])
+
+    for w in range(min(args.warmup, 1)):       # one warm-up pair bounds the run time
+        one(w)
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        one(1 + s)
+    dt = time.perf_counter() - t0
+    val = args.steps / dt
+    sample = f"each step = 1 pair of the workload (N={args.n}); {args.steps} steps after 1 warm-up pair"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "family": args.family, "pairs_per_step": 1, "N": args.n,
+                   "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    from pointdsc_b200 import PointDSC, _cabi
+    _cabi.check_device()
+    cfg, batch, sd = make_inputs(args, rank)
+    model = PointDSC(num_layers=NUM_LAYERS, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
+                     nms_radius=cfg["nms_radius"]).eval()
+    model.load_state_dict(sd, strict=True)
+    model = model.to(dev)
+    model.attn_mode = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "fp16": _cabi.ATTN_FP16}[args.mode]
+
+    keys = ("corr_pos", "src_keypts", "tgt_keypts")
+    host = {k: batch[k].pin_memory() for k in keys}
+    resident = {k: batch[k].to(dev) for k in keys}
+    resident["testing"] = True
+    h2d_bytes = sum(host[k].numel() * 4 for k in keys)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # -------- resident-input arm (value) ---------------------------------------------------------
+    attn_events = []
+    orig_attn = _cabi.nonlocal_attn
+
+    def timed_attn(*a, **kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = orig_attn(*a, **kw)
+        e1.record()
+        attn_events.append((e0, e1))
+        return out
+
+    def step_resident():
+        flush.zero_()                       # L2 flush between steps (inside the timed region)
+        return model(resident)
+
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    _cabi.nonlocal_attn = timed_attn        # CUDA events around the dominant kernel, same stream
+    launches0 = _cabi.kernel_launches()
+    s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    s_ev.record()
+    for _ in range(args.steps):
+        res = step_resident()
+    e_ev.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = _cabi.kernel_launches() - launches0
+    _cabi.nonlocal_attn = orig_attn
+    dev_ms = s_ev.elapsed_time(e_ev)
+    attn_ms = [a.elapsed_time(b) for a, b in attn_events]
+
+    # -------- end-to-end arm (host buffers, copies inside the timed region) ----------------------
+    out_trans = torch.empty(args.pairs, 4, 4, dtype=torch.float32).pin_memory()
+    out_labels = torch.empty(args.pairs, args.n, dtype=torch.float32).pin_memory()
+    d2h_bytes = out_trans.numel() * 4 + out_labels.numel() * 4
+
+    def step_e2e():
+        flush.zero_()
+        data = {k: host[k].to(dev, non_blocking=True) for k in keys}
+        data["testing"] = True
+        r = model(data)
+        out_trans.copy_(r["final_trans"], non_blocking=True)
+        out_labels.copy_(r["final_labels"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller reads the result
+        return r
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s2.record()
+    for _ in range(args.steps):
+        step_e2e()
+    e2.record()
+    barrier()
+    e2e_ms = s2.elapsed_time(e2)
+    clocks = sampler.stop()
+
+    # -------- reduce over ranks (max time) ---------------------------------------------------------
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    total_pairs = args.pairs * world * args.steps
+    value = total_pairs / (dev_ms / 1e3)
+    e2e_value = total_pairs / (e2e_ms / 1e3)
+
+    if rank == 0:
+        pk = peaks()
+        flops_per_launch = 4.0 * args.n * args.n * C * args.pairs          # QK^T + PV, per layer, per batch
+        avg_attn_ms = sum(attn_ms) / max(1, len(attn_ms))
+        achieved = flops_per_launch / (avg_attn_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "kernel": f"pdsc_nonlocal_attn[{args.mode}]", "achieved": achieved,
+                    "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_sustained"],
+                    "traffic": None, "peak_source": pk["source"] + ", bf16 sustained",
+                    "algorithmic_flops_per_launch": flops_per_launch, "avg_launch_ms": avg_attn_ms,
+                    "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32" if args.mode == "fp32" else "f16x2-split/f32-accum",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args), "family": args.family, "pairs_per_step_per_gpu": args.pairs,
+                       "N": args.n, "num_layers": NUM_LAYERS, "attn_mode": args.mode,
+                       "l2": "256 MB buffer rewritten between steps (inside the timed region)",
+                       "parallelism": f"pairs sharded over {world} GPU(s), no communication"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": roofline,
+            "wall_s_timed_region": t_wall,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, cfg, batch, sd, args.cpu_pairs)
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
