@@ -12,3 +12,8 @@ tail -5 gpurun_out/smoke.log
 echo "=== bench"
 timeout 900 python bench.py ${BENCH_ARGS} > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
 cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+if [ -n "${NCU_LAUNCHES}" ]; then
+echo "=== ncu launch list"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c ${NCU_LAUNCHES} --csv --log-file gpurun_out/launches.csv python bench.py ${NCU_BENCH_ARGS} > gpurun_out/ncu.log 2>&1; echo "ncu exit $?"
+tail -3 gpurun_out/ncu.log
+fi
