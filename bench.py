@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--pairs", type=int, default=16, help="pairs per step per GPU")
     ap.add_argument("--n", type=int, default=5000, help="correspondences per pair")
     ap.add_argument("--family", default="3dmatch", choices=["3dmatch", "kitti"])
-    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "fp32"), choices=["fp32", "split16", "fp16"])
+    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "fp16"])
     ap.add_argument("--cpu-pairs", type=int, default=3, help="pairs in the cpu_baseline sample (first is warm-up)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

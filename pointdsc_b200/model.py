@@ -100,7 +100,7 @@ class PointDSC(nn.Module):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
         # kernel selection for the attention contraction (include/pointdsc_b200.h PDSC_ATTN_*)
-        self.attn_mode = _MODE_NAMES[os.environ.get("POINTDSC_ATTN_MODE", "fp32")]
+        self.attn_mode = _MODE_NAMES[os.environ.get("POINTDSC_ATTN_MODE", "split16")]
         self._packed = None
         self._ws = _cabi.Workspace()
 

@@ -9,7 +9,7 @@ from parity import CONF_TOL, assert_labels_match, assert_trans_close, golden_mod
 
 pytestmark = pytest.mark.gpu
 
-MODES = ["fp32"]
+MODES = ["fp32", "split16"]
 
 
 def _mode(name):

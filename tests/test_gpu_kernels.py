@@ -257,3 +257,63 @@ def test_compat_matvec_row_sharding_is_exact():
     full = _cabi.compat_matvec(s, t, v, 0, 1000, 1.2)
     parts = [_cabi.compat_matvec(s, t, v, r0, r1, 1.2) for r0, r1 in [(0, 250), (250, 500), (500, 777), (777, 1000)]]
     assert torch.equal(torch.cat(parts), full)
+
+
+# ----------------------------------------------------------- (a) attention on tcgen05 (split fp16)
+def _attn_ref(qkv, src, tgt, sigma):
+    C = qkv.shape[-1] // 3
+    outs = []
+    for b in range(qkv.shape[0]):
+        _, compat = restate.spatial_compatibility(src[b:b + 1], tgt[b:b + 1], torch.tensor([sigma]))
+        outs.append(restate.nonlocal_message(qkv[b:b + 1, :, :C].permute(0, 2, 1), qkv[b:b + 1, :, C:2 * C].permute(0, 2, 1),
+                                             qkv[b:b + 1, :, 2 * C:].permute(0, 2, 1), compat).permute(0, 2, 1))
+    return torch.cat(outs)
+
+
+@pytest.mark.parametrize("N", [128, 1, 100, 129, 256, 700])
+def test_attention_split16_vs_oracle(N):
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(1000 + N)
+    C, B = 128, 2
+    qkv = torch.randn(B, N, 3 * C, generator=g)
+    src = torch.rand(B, N, 3, generator=g)
+    tgt = src + 0.05 * torch.randn(B, N, 3, generator=g)
+    d = cu(qkv)
+    out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1, mode=_cabi.ATTN_SPLIT16)
+    torch.cuda.synchronize()
+    ref = _attn_ref(qkv, src, tgt, 0.1)
+    err = (out.cpu() - ref).abs().max().item()
+    print(f"split16 attention N={N}: max abs err {err:.3e}")
+    assert err < 5e-5
+
+
+def test_attention_split16_large_logits_trigger_rescale():
+    """Row maxima that keep growing along the key axis exercise the lazy O rescale."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(77)
+    C, B, N = 128, 1, 640
+    qkv = torch.randn(B, N, 3 * C, generator=g)
+    qkv[:, :, C:2 * C] *= torch.linspace(0.2, 6.0, N)[None, :, None]     # later keys -> larger logits
+    src = torch.rand(B, N, 3, generator=g) * 0.05                      # everything mutually compatible
+    tgt = src.clone()
+    d = cu(qkv)
+    out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1, mode=_cabi.ATTN_SPLIT16)
+    ref = _attn_ref(qkv, src, tgt, 0.1)
+    err = (out.cpu() - ref).abs().max().item()
+    print(f"split16 attention with growing maxima: max abs err {err:.3e}")
+    assert err < 2e-4
+
+
+@pytest.mark.parametrize("case", SMALL)
+def test_attention_split16_on_oracle_layers(case):
+    from pointdsc_b200 import _cabi
+    meta, g, sd, out = oracle_run(case)
+    sig = float(sd["sigma_spat"])
+    worst = 0.0
+    for tap in out["layer_taps"]:
+        q, k, v = [cu(tap[n].permute(0, 2, 1)) for n in ("q", "k", "v")]
+        msg = _cabi.nonlocal_attn(q, k, v, cu(g["src_keypts"]), cu(g["tgt_keypts"]), sig, mode=_cabi.ATTN_SPLIT16)
+        ref = tap["msg"].permute(0, 2, 1)
+        worst = max(worst, float((msg.cpu() - ref).abs().max()) / max(1.0, float(ref.abs().max())))
+    print(f"{case}: split16 attention worst relative-to-scale error over layers {worst:.3e}")
+    assert worst < 5e-5
