@@ -13,14 +13,16 @@
 // PDSC_ATTN_FP16 issues only hi*hi.
 //
 // One CTA = 128 query rows of one pair, looping over 128-key tiles:
-//   warp 0      producer: cp.async.bulk of the pre-swizzled Q / K / V^T tiles and key points
+//   warp 0      producer: cp.async.bulk of the pre-swizzled Q / K tiles and key points
 //   warp 1      MMA issuer (one elected lane), owns the TMEM allocation
-//   warps 2-9   two softmax warpgroups; thread <-> query row, warpgroup g takes keys [64g,64g+64)
+//   warp 2      producer of the V^T tiles
+//   warps 3..   NWG softmax warpgroups; thread <-> query row, warpgroup g takes keys [g*128/NWG, ...)
 // S is double buffered in TMEM so S(j+1)=QK(j+1)^T overlaps softmax(j); PV(j) follows softmax(j).
 #include "common.cuh"
 #include "sm100.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 namespace pdsc {
 
@@ -29,19 +31,20 @@ using namespace sm100;
 constexpr int TC_C = 128;            // channels (head dim); kernels are built for C = 128
 constexpr int TC_BM = 128;           // query rows per CTA
 constexpr int TC_BN = 128;           // keys per tile
-constexpr int TC_THREADS = 320;
+constexpr int TC_MAX_WG = 4;          // softmax warpgroups (2 or 4), keys per warpgroup = 128 / NWG
 constexpr uint32_t TC_BLOCK_BYTES = 128 * 128;            // one swizzled block: 128 rows x 64 fp16
 constexpr uint32_t TC_TILE_BYTES = 4 * TC_BLOCK_BYTES;    // [hi|lo][k-chunk 0|1]
-constexpr uint32_t TC_PTS_BYTES = TC_BN * 8 * 4;          // src xyz _, tgt xyz _ per key
+constexpr uint32_t TC_PTS_FLOATS = (TC_BN / 2) * 12;      // per key PAIR: sx0 sx1 sy0 sy1 sz0 sz1 tx0 tx1 ty0 ty1 tz0 tz1
+constexpr uint32_t TC_PTS_BYTES = TC_PTS_FLOATS * 4;
 constexpr float TC_RESCALE_LOG2 = 8.0f;                   // lazy rescale threshold (log2 units)
 
 struct TcSmem {
     uint8_t q[TC_TILE_BYTES];
     uint8_t k[TC_TILE_BYTES];
     uint8_t v[TC_TILE_BYTES];
-    float pts[2][TC_BN][8];
-    float smax[2][2][TC_BM];
-    float lsum[2][TC_BM];
+    float4 pts[2][TC_BN / 2][3];
+    float smax[2][TC_MAX_WG][TC_BM];
+    float lsum[TC_MAX_WG][TC_BM];
     uint64_t q_full, k_full, k_empty, v_full, v_empty, pv_done;
     uint64_t s_full[2], p_full[2], pts_full[2];
     uint32_t tmem_base;
@@ -124,13 +127,23 @@ __global__ void __launch_bounds__(256) attn_prep_kernel(const float* __restrict_
         *reinterpret_cast<uint4*>(vd + 2 * TC_BLOCK_BYTES + off) = lo;
     }
     if (threadIdx.x < TC_BN) {
+        // packed-pair SoA layout so the softmax loop can use FADD2/FFMA2 on two keys at once
         const int n = min(n0 + (int)threadIdx.x, N - 1);
         const float* s = src + ((size_t)b * N + n) * 3;
         const float* g = tgt + ((size_t)b * N + n) * 3;
-        float4* d = reinterpret_cast<float4*>(Pw + (tile * TC_BN + threadIdx.x) * 8);
-        d[0] = make_float4(s[0], s[1], s[2], 0.f);
-        d[1] = make_float4(g[0], g[1], g[2], 0.f);
+        float* d = Pw + tile * TC_PTS_FLOATS + (threadIdx.x >> 1) * 12 + (threadIdx.x & 1);
+        d[0] = s[0]; d[2] = s[1]; d[4] = s[2]; d[6] = g[0]; d[8] = g[1]; d[10] = g[2];
     }
+}
+
+// One 64 KB tile as several bulk copies in flight at once (a single copy is served serially).
+#ifndef TC_COPY_SPLIT
+#define TC_COPY_SPLIT 1
+#endif
+__device__ __forceinline__ void bulk_tile(uint8_t* dst, const uint8_t* src, uint64_t* bar) {
+    constexpr uint32_t part = TC_TILE_BYTES / TC_COPY_SPLIT;
+#pragma unroll
+    for (int i = 0; i < TC_COPY_SPLIT; ++i) bulk_g2s(dst + i * part, src + i * part, part, bar);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -154,15 +167,16 @@ __device__ __forceinline__ void issue_qk(uint32_t d_tmem, uint32_t a_base, uint3
     }
 }
 // O[128x128ch] (+)= P[128 x 128 keys] * Vt[128ch x 128 keys]^T, P from TMEM (packed fp16, hi at
-// p_tmem, lo 32 columns further, each warpgroup's 64 keys in its own 64-column half).
+// p_tmem, lo KW/2 columns further, each warpgroup's KW keys inside its own KW-column slice of S).
+template <int KW>
 __device__ __forceinline__ void issue_pv(uint32_t o_tmem, uint32_t p_tmem, uint32_t v_base, int terms, uint32_t acc) {
     constexpr uint32_t idesc = umma_idesc_f16(128, 128);
     for (int term = 0; term < terms; ++term) {
-        const uint32_t p_part = (term == 2) ? 32u : 0u;
+        const uint32_t p_part = (term == 2) ? (uint32_t)(KW / 2) : 0u;
         const uint32_t v_part = (term == 1) ? 2u * TC_BLOCK_BYTES : 0u;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
-            const uint32_t a = p_tmem + (uint32_t)(kk >> 2) * 64u + (uint32_t)(kk & 3) * 8u + p_part;
+            const uint32_t a = p_tmem + (uint32_t)((kk * 16) / KW) * (uint32_t)KW + (uint32_t)((kk * 16) % KW) / 2u + p_part;
             const uint32_t koff = (uint32_t)(kk >> 2) * TC_BLOCK_BYTES + (uint32_t)(kk & 3) * 32u;
             umma_ts(o_tmem, a, umma_desc_sw128_kmajor(v_base + v_part + koff), idesc, acc);
             acc = 1;
@@ -173,23 +187,27 @@ __device__ __forceinline__ void issue_pv(uint32_t o_tmem, uint32_t p_tmem, uint3
 // ------------------------------------------------------------------------------------------------
 // Main kernel
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* __restrict__ Qw,
+template <int NWG>
+__global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_t* __restrict__ Qw,
                                                                 const uint8_t* __restrict__ Kw,
                                                                 const uint8_t* __restrict__ Vw,
                                                                 const float* __restrict__ Pw, float* __restrict__ out,
                                                                 int64_t ld_out, int N, int NT, float inv_sig2,
-                                                                int terms) {
+                                                                int terms, long long* __restrict__ trace) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // the 128B swizzle is anchored at 1024-byte boundaries of the shared window
     TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
     const int qt = blockIdx.x, b = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t tile0 = (size_t)b * NT;
+    // optional timeline of CTA (0,0) (PDSC_ATTN_TRACE): trace[j*8 + event] = SM clock
+    const bool tracing = trace != nullptr && qt == 0 && b == 0;
+#define TC_TRACE(j, ev) do { if (tracing) trace[(j) * 8 + (ev)] = clock64(); } while (0)
 
     if (threadIdx.x == 0) {
         mbar_init(&sm.q_full, 1); mbar_init(&sm.k_full, 1); mbar_init(&sm.k_empty, 1);
         mbar_init(&sm.v_full, 1); mbar_init(&sm.v_empty, 1); mbar_init(&sm.pv_done, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], 8); mbar_init(&sm.pts_full[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], NWG * 4); mbar_init(&sm.pts_full[i], 1); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
@@ -200,21 +218,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
     const uint32_t TM_S = 0, TM_O = 256;
 
     if (warp == 0) {
-        // ============================== producer ==============================
+        // ============================== producer: Q, K tiles, key points ==============================
         if (lane == 0) {
             mbar_arrive_expect_tx(&sm.q_full, TC_TILE_BYTES);
-            bulk_g2s(sm.q, Qw + (tile0 + qt) * TC_TILE_BYTES, TC_TILE_BYTES, &sm.q_full);
+            bulk_tile(sm.q, Qw + (tile0 + qt) * TC_TILE_BYTES, &sm.q_full);
             for (int j = 0; j < NT; ++j) {
                 const int buf = j & 1;
-                if (j > 0) mbar_wait(&sm.k_empty, (j - 1) & 1);
+                if (j > 0) mbar_wait(&sm.k_empty, (j - 1) & 1);          // S(j-1) has consumed the K buffer
+                TC_TRACE(j, 0);
                 mbar_arrive_expect_tx(&sm.k_full, TC_TILE_BYTES);
-                bulk_g2s(sm.k, Kw + (tile0 + j) * TC_TILE_BYTES, TC_TILE_BYTES, &sm.k_full);
-                if (j >= 2) mbar_wait(&sm.p_full[buf], ((j - 2) >> 1) & 1);
+                bulk_tile(sm.k, Kw + (tile0 + j) * TC_TILE_BYTES, &sm.k_full);
+                if (j >= 2) mbar_wait(&sm.p_full[buf], ((j - 2) >> 1) & 1);   // softmax(j-2) is done with pts[buf]
                 mbar_arrive_expect_tx(&sm.pts_full[buf], TC_PTS_BYTES);
-                bulk_g2s(sm.pts[buf], Pw + (tile0 + j) * TC_BN * 8, TC_PTS_BYTES, &sm.pts_full[buf]);
-                if (j > 0) mbar_wait(&sm.v_empty, (j - 1) & 1);
+                bulk_g2s(sm.pts[buf], Pw + (tile0 + j) * TC_PTS_FLOATS, TC_PTS_BYTES, &sm.pts_full[buf]);
+            }
+        }
+    } else if (warp == 2) {
+        // ============================== producer: V^T tiles (own warp: never waits behind K) ==========
+        if (lane == 0) {
+            for (int j = 0; j < NT; ++j) {
+                if (j > 0) mbar_wait(&sm.v_empty, (j - 1) & 1);          // PV(j-1) has consumed the V buffer
+                TC_TRACE(j, 1);
                 mbar_arrive_expect_tx(&sm.v_full, TC_TILE_BYTES);
-                bulk_g2s(sm.v, Vw + (tile0 + j) * TC_TILE_BYTES, TC_TILE_BYTES, &sm.v_full);
+                bulk_tile(sm.v, Vw + (tile0 + j) * TC_TILE_BYTES, &sm.v_full);
             }
         }
     } else if (warp == 1) {
@@ -231,6 +257,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
                 const int buf = j & 1;
                 if (j + 1 < NT) {
                     mbar_wait(&sm.k_full, (j + 1) & 1);
+                    TC_TRACE(j + 1, 2);
                     tc_fence_after();
                     issue_qk(tmem + TM_S + (uint32_t)(buf ^ 1) * 128u, q_addr, k_addr, terms);
                     umma_commit(&sm.s_full[buf ^ 1]);
@@ -238,21 +265,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
                 }
                 mbar_wait(&sm.p_full[buf], (j >> 1) & 1);
                 mbar_wait(&sm.v_full, j & 1);
+                TC_TRACE(j, 3);
                 tc_fence_after();
-                issue_pv(tmem + TM_O, tmem + TM_S + (uint32_t)buf * 128u, v_addr, terms, j > 0 ? 1u : 0u);
+                issue_pv<128 / NWG>(tmem + TM_O, tmem + TM_S + (uint32_t)buf * 128u, v_addr, terms, j > 0 ? 1u : 0u);
                 umma_commit(&sm.v_empty);
                 umma_commit(&sm.pv_done);
             }
         }
     } else {
         // ============================== softmax warpgroups ==============================
-        const int wg = (warp - 2) >> 2;              // 0: keys 0..63 of a tile, 1: keys 64..127
+        constexpr int KW = TC_BN / NWG;              // keys of a tile handled by one warpgroup
+        constexpr int NP = KW / 2;                   // ... as key pairs
+        constexpr int OW = TC_C / NWG;               // O columns a warpgroup rescales / writes out
+        const int wg = (warp - 3) >> 2;
         const int quarter = warp & 3;                // TMEM lane quarter this warp may access
         const int row = quarter * 32 + lane;         // query row inside the CTA tile
         const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
         const int qrow = min(qt * TC_BM + row, N - 1);
-        const float* qp = Pw + ((tile0 + (qrow >> 7)) * TC_BN + (qrow & 127)) * 8;
-        const float qsx = qp[0], qsy = qp[1], qsz = qp[2], qtx = qp[4], qty = qp[5], qtz = qp[6];
+        const float* qp = Pw + (tile0 + (qrow >> 7)) * TC_PTS_FLOATS + ((qrow & 127) >> 1) * 12 + (qrow & 1);
+        const float2 qsx = make_float2(qp[0], qp[0]), qsy = make_float2(qp[2], qp[2]), qsz = make_float2(qp[4], qp[4]);
+        const float2 qtx = make_float2(qp[6], qp[6]), qty = make_float2(qp[8], qp[8]), qtz = make_float2(qp[10], qp[10]);
+        const float2 neg_inv2 = make_float2(-inv_sig2, -inv_sig2), one2 = make_float2(1.0f, 1.0f);
         float m = -INFINITY, l = 0.f;
 
         for (int j = 0; j < NT; ++j) {
@@ -260,37 +293,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
             const uint32_t par = (j >> 1) & 1;
             mbar_wait(&sm.pts_full[buf], par);
             mbar_wait(&sm.s_full[buf], par);
+            if (threadIdx.x == 96) TC_TRACE(j, 4);
             tc_fence_after();
-            const uint32_t s_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)wg * 64u;
+            const uint32_t s_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)(wg * KW);
             const int nvalid = N - j * TC_BN;        // keys of this tile that exist
-            float x[64];
+            float2 x[NP];
             float tmax = -INFINITY;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < KW / 32; ++h) {
                 uint32_t r[32];
                 tmem_ld32(s_col + h * 32, r);
                 tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const int key = wg * 64 + h * 32 + i;
-                    const float4 ks = *reinterpret_cast<const float4*>(&sm.pts[buf][key][0]);
-                    const float4 kt = *reinterpret_cast<const float4*>(&sm.pts[buf][key][4]);
-                    float dx = qsx - ks.x, dy = qsy - ks.y, dz = qsz - ks.z;
-                    const float ds = fast_sqrt(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
-                    dx = qtx - kt.x; dy = qty - kt.y; dz = qtz - kt.z;
-                    const float dt = fast_sqrt(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
-                    const float c = ds - dt;
-                    const float compat = fmaxf(fmaf(-c * c, inv_sig2, 1.0f), 0.0f);
-                    float xv = compat * __uint_as_float(r[i]);
-                    if (key >= nvalid) xv = -INFINITY;
-                    x[h * 32 + i] = xv;
-                    tmax = fmaxf(tmax, xv);
+                for (int i = 0; i < 16; ++i) {
+                    const int kp = wg * NP + h * 16 + i;     // key pair inside the tile
+                    const float4 pa = sm.pts[buf][kp][0], pb = sm.pts[buf][kp][1], pc = sm.pts[buf][kp][2];
+                    float2 dx = __fadd2_rn(qsx, make_float2(-pa.x, -pa.y));
+                    float2 dy = __fadd2_rn(qsy, make_float2(-pa.z, -pa.w));
+                    float2 dz = __fadd2_rn(qsz, make_float2(-pb.x, -pb.y));
+                    float2 a2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+                    const float2 ds = make_float2(fast_sqrt(a2.x), fast_sqrt(a2.y));
+                    dx = __fadd2_rn(qtx, make_float2(-pb.z, -pb.w));
+                    dy = __fadd2_rn(qty, make_float2(-pc.x, -pc.y));
+                    dz = __fadd2_rn(qtz, make_float2(-pc.z, -pc.w));
+                    a2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+                    const float2 dt = make_float2(fast_sqrt(a2.x), fast_sqrt(a2.y));
+                    const float2 c = __fadd2_rn(ds, make_float2(-dt.x, -dt.y));
+                    float2 w = __ffma2_rn(__fmul2_rn(c, c), neg_inv2, one2);
+                    w.x = fmaxf(w.x, 0.0f);
+                    w.y = fmaxf(w.y, 0.0f);
+                    const float2 xv = __fmul2_rn(w, make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])));
+                    x[h * 16 + i] = xv;
+                    tmax = fmaxf(tmax, fmaxf(xv.x, xv.y));
                 }
             }
-            // tile row max across the two warpgroups
+            if (nvalid < TC_BN) {                    // last, partial tile: keys past N do not exist
+                tmax = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < NP; ++i) {
+                    const int key = wg * KW + 2 * i;
+                    if (key >= nvalid) x[i].x = -INFINITY;
+                    if (key + 1 >= nvalid) x[i].y = -INFINITY;
+                    tmax = fmaxf(tmax, fmaxf(x[i].x, x[i].y));
+                }
+            }
+            if (threadIdx.x == 96) TC_TRACE(j, 5);
+            // tile row max across the warpgroups
             sm.smax[buf][wg][row] = tmax;
-            named_bar_sync(1, 256);
-            tmax = fmaxf(tmax, sm.smax[buf][wg ^ 1][row]);
+            named_bar_sync(1, NWG * 128);
+#pragma unroll
+            for (int g = 0; g < NWG; ++g) tmax = fmaxf(tmax, sm.smax[buf][g][row]);
             // lazy rescale: keep the old reference max unless the row max grew by more than 2^8
             if (j == 0) {
                 m = tmax;
@@ -298,14 +350,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
                 // PV(j-1) has finished accumulating into O.  Waited for on every tile (normally already
                 // complete here) so that no waiter ever lags two phases behind the barrier.
                 mbar_wait(&sm.pv_done, (j - 1) & 1);
+                if (threadIdx.x == 96) TC_TRACE(j, 6);
                 const bool need = tmax > m + TC_RESCALE_LOG2;
                 if (__any_sync(0xffffffffu, need)) {
                     tc_fence_after();
                     const float f = need ? fast_exp2(m - tmax) : 1.0f;
                     if (need) { m = tmax; l *= f; }
-                    const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)wg * 64u;
+                    const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)(wg * OW);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
+                    for (int h = 0; h < OW / 32; ++h) {
                         uint32_t r[32];
                         tmem_ld32(o_col + h * 32, r);
                         tmem_ld_wait();
@@ -317,40 +370,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* _
                 }
             }
             // P = exp2(x - m), split into fp16 hi/lo, packed two keys per TMEM column
-            const uint32_t p_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)wg * 64u;
-            float psum = 0.f;
+            const uint32_t p_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)(wg * KW);
+            float2 psum = make_float2(0.f, 0.f);
+            const float2 neg_m = make_float2(-m, -m);
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
+            for (int g = 0; g < NP / 16; ++g) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const float p0 = fast_exp2(x[g * 32 + 2 * i] - m);
-                    const float p1 = fast_exp2(x[g * 32 + 2 * i + 1] - m);
-                    psum += p0 + p1;
-                    hi[i] = pack_half2(p0, p1);
+                    const float2 e = __fadd2_rn(x[g * 16 + i], neg_m);
+                    const float2 p = make_float2(fast_exp2(e.x), fast_exp2(e.y));
+                    psum = __fadd2_rn(psum, p);
+                    hi[i] = pack_half2(p.x, p.y);
                     const float2 back = unpack_half2(hi[i]);
-                    lo[i] = pack_half2(p0 - back.x, p1 - back.y);
+                    const float2 rem = __fadd2_rn(p, make_float2(-back.x, -back.y));
+                    lo[i] = pack_half2(rem.x, rem.y);
                 }
                 tmem_st16(p_col + g * 16, hi);
-                if (terms > 1) tmem_st16(p_col + 32 + g * 16, lo);
+                if (terms > 1) tmem_st16(p_col + NP + g * 16, lo);
             }
-            l += psum;
+            l += psum.x + psum.y;
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.p_full[buf]);
+            if (threadIdx.x == 96) TC_TRACE(j, 7);
         }
         // ---- epilogue: msg = O / l ----
         sm.lsum[wg][row] = l;
         mbar_wait(&sm.pv_done, (NT - 1) & 1);
         tc_fence_after();
-        named_bar_sync(1, 256);
-        const float inv_l = 1.0f / (l + sm.lsum[wg ^ 1][row]);
-        const int grow = qt * TC_BM + row;
-        const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)wg * 64u;
-        float* orow = out + ((size_t)b * N + min(grow, N - 1)) * ld_out + wg * 64;
+        named_bar_sync(1, NWG * 128);
+        float lt = 0.f;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        for (int g = 0; g < NWG; ++g) lt += sm.lsum[g][row];
+        const float inv_l = 1.0f / lt;
+        const int grow = qt * TC_BM + row;
+        const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)(wg * OW);
+        float* orow = out + ((size_t)b * N + min(grow, N - 1)) * ld_out + wg * OW;
+#pragma unroll
+        for (int h = 0; h < OW / 32; ++h) {
             uint32_t r[32];
             tmem_ld32(o_col + h * 32, r);
             tmem_ld_wait();
@@ -393,17 +452,39 @@ int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, c
     uint8_t* Kw = Qw + tiles * TC_TILE_BYTES;
     uint8_t* Vw = Kw + tiles * TC_TILE_BYTES;
     float* Pw = reinterpret_cast<float*>(Vw + tiles * TC_TILE_BYTES);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static int nwg = 0;
+    if (nwg == 0) {
+        const char* e = getenv("PDSC_ATTN_NWG");
+        nwg = (e && atoi(e) == 2) ? 2 : 4;
         cudaFuncSetAttribute(attn_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
-        cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
-        attr_set = true;
+        cudaFuncSetAttribute(attn_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
+        cudaFuncSetAttribute(attn_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
     }
     const float qscale = 1.4426950408889634f / sqrtf((float)C);
     attn_prep_kernel<<<dim3(NT, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, NT, qscale, Qw, Kw, Vw, Pw);
     const float inv_sig2 = 1.0f / (sigma_spat * sigma_spat);
-    attn_tc_kernel<<<dim3(NT, B), TC_THREADS, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2,
-                                                                          mode == PDSC_ATTN_SPLIT16 ? 3 : 1);
+    const int terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
+    long long* trace = nullptr;
+    const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA (0,0)
+    if (trace_path) { cudaMalloc(&trace, sizeof(long long) * 8 * NT); cudaMemset(trace, 0, sizeof(long long) * 8 * NT); }
+    if (nwg == 2)
+        attn_tc_kernel<2><<<dim3(NT, B), 96 + 2 * 128, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2, terms, trace);
+    else
+        attn_tc_kernel<4><<<dim3(NT, B), 96 + 4 * 128, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2, terms, trace);
+    if (trace) {
+        cudaStreamSynchronize(st);
+        long long* h = (long long*)malloc(sizeof(long long) * 8 * NT);
+        cudaMemcpy(h, trace, sizeof(long long) * 8 * NT, cudaMemcpyDeviceToHost);
+        FILE* f = fopen(trace_path, "w");
+        if (f) {
+            for (int j = 0; j < NT; ++j) {
+                for (int e = 0; e < 8; ++e) fprintf(f, "%lld%c", h[j * 8 + e] ? h[j * 8 + e] - h[0] : -1, e == 7 ? '\n' : ' ');
+            }
+            fclose(f);
+        }
+        free(h);
+        cudaFree(trace);
+    }
     count_launches(2);
     return check_launch("nonlocal_attn(tcgen05)");
 }

@@ -1,0 +1,25 @@
+"""Runs the attention kernel alone on the bench shape (for ncu): python scripts/prof_attn.py [mode] [B] [N] [reps]"""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from pointdsc_b200 import _cabi
+mode = {"fp32": 0, "split16": 1, "fp16": 2}[sys.argv[1] if len(sys.argv) > 1 else "split16"]
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 16
+N = int(sys.argv[3]) if len(sys.argv) > 3 else 5000
+reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
+g = torch.Generator().manual_seed(0)
+qkv = torch.randn(B, N, 384, generator=g).cuda()
+src = (torch.rand(B, N, 3, generator=g) * 3).cuda()
+tgt = (torch.rand(B, N, 3, generator=g) * 3).cuda()
+C = 128
+for _ in range(2):
+    out = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=mode)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(reps):
+    out = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=mode)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / reps
+print(f"mode {mode} B={B} N={N}: {ms:.3f} ms per call (prep+main), {4.0 * N * N * C * B / ms / 1e9:.1f} TFLOP/s algorithmic")
