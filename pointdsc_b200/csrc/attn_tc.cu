@@ -31,7 +31,7 @@ using namespace sm100;
 constexpr int TC_C = 128;            // channels (head dim); kernels are built for C = 128
 constexpr int TC_BM = 128;           // query rows per CTA
 constexpr int TC_BN = 128;           // keys per tile
-constexpr int TC_MAX_WG = 4;          // softmax warpgroups (2 or 4), keys per warpgroup = 128 / NWG
+constexpr int TC_THREADS = 96 + 2 * 128;   // K producer, MMA issuer, V producer, 2 softmax warpgroups
 constexpr uint32_t TC_BLOCK_BYTES = 128 * 128;            // one swizzled block: 128 rows x 64 fp16
 constexpr uint32_t TC_TILE_BYTES = 4 * TC_BLOCK_BYTES;    // [hi|lo][k-chunk 0|1]
 constexpr uint32_t TC_PTS_FLOATS = (TC_BN / 2) * 12;      // per key PAIR: sx0 sx1 sy0 sy1 sz0 sz1 tx0 tx1 ty0 ty1 tz0 tz1
@@ -43,10 +43,10 @@ struct TcSmem {
     uint8_t k[TC_TILE_BYTES];
     uint8_t v[TC_TILE_BYTES];
     float4 pts[2][TC_BN / 2][3];
-    float smax[2][TC_MAX_WG][TC_BM];
-    float lsum[TC_MAX_WG][TC_BM];
-    uint64_t q_full, k_full, k_empty, v_full, v_empty, pv_done;
-    uint64_t s_full[2], p_full[2], pts_full[2];
+    float mfin[2][TC_BM];
+    float lsum[2][TC_BM];
+    uint64_t q_full, k_full, k_empty, v_full, v_empty;
+    uint64_t s_full[2], pts_full[2], pv_done[2], p_full[2][2];
     uint32_t tmem_base;
 };
 
@@ -166,29 +166,30 @@ __device__ __forceinline__ void issue_qk(uint32_t d_tmem, uint32_t a_base, uint3
         }
     }
 }
-// O[128x128ch] (+)= P[128 x 128 keys] * Vt[128ch x 128 keys]^T, P from TMEM (packed fp16, hi at
-// p_tmem, lo KW/2 columns further, each warpgroup's KW keys inside its own KW-column slice of S).
-template <int KW>
-__device__ __forceinline__ void issue_pv(uint32_t o_tmem, uint32_t p_tmem, uint32_t v_base, int terms, uint32_t acc) {
+// O_g[128x128ch] (+)= P_g[128 x 64 keys] * Vt[128ch x 64 keys]^T for the 64 keys of warpgroup g.
+// P comes from TMEM (packed fp16: hi at p_tmem, lo 32 columns further, inside the warpgroup's own
+// 64-column half of the S buffer), V^T from the g-th 64-key block in shared memory.
+__device__ __forceinline__ void issue_pv_half(uint32_t o_tmem, uint32_t p_tmem, uint32_t v_block, int terms, uint32_t acc) {
     constexpr uint32_t idesc = umma_idesc_f16(128, 128);
     for (int term = 0; term < terms; ++term) {
-        const uint32_t p_part = (term == 2) ? (uint32_t)(KW / 2) : 0u;
+        const uint32_t p_part = (term == 2) ? 32u : 0u;
         const uint32_t v_part = (term == 1) ? 2u * TC_BLOCK_BYTES : 0u;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-            const uint32_t a = p_tmem + (uint32_t)((kk * 16) / KW) * (uint32_t)KW + (uint32_t)((kk * 16) % KW) / 2u + p_part;
-            const uint32_t koff = (uint32_t)(kk >> 2) * TC_BLOCK_BYTES + (uint32_t)(kk & 3) * 32u;
-            umma_ts(o_tmem, a, umma_desc_sw128_kmajor(v_base + v_part + koff), idesc, acc);
+        for (int kk = 0; kk < 4; ++kk) {
+            umma_ts(o_tmem, p_tmem + (uint32_t)kk * 8u + p_part, umma_desc_sw128_kmajor(v_block + v_part + (uint32_t)kk * 32u),
+                    idesc, acc);
             acc = 1;
         }
     }
 }
 
 // ------------------------------------------------------------------------------------------------
-// Main kernel
+// Main kernel.  TMEM columns: S0 [0,128) S1 [128,256) O_0 [256,384) O_1 [384,512).
+// The two softmax warpgroups are fully independent: warpgroup g owns keys [64g,64g+64) of every
+// tile, its own running max / sum and its own accumulator O_g; they only meet in the epilogue
+// (msg = (O_0 2^(m_0-M) + O_1 2^(m_1-M)) / L).  No per-tile exchange, no CTA-wide barrier.
 // ------------------------------------------------------------------------------------------------
-template <int NWG>
-__global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_t* __restrict__ Qw,
+__global__ void __launch_bounds__(TC_THREADS, 1) attn_tc_kernel(const uint8_t* __restrict__ Qw,
                                                                 const uint8_t* __restrict__ Kw,
                                                                 const uint8_t* __restrict__ Vw,
                                                                 const float* __restrict__ Pw, float* __restrict__ out,
@@ -206,8 +207,11 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
 
     if (threadIdx.x == 0) {
         mbar_init(&sm.q_full, 1); mbar_init(&sm.k_full, 1); mbar_init(&sm.k_empty, 1);
-        mbar_init(&sm.v_full, 1); mbar_init(&sm.v_empty, 1); mbar_init(&sm.pv_done, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], NWG * 4); mbar_init(&sm.pts_full[i], 1); }
+        mbar_init(&sm.v_full, 1); mbar_init(&sm.v_empty, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&sm.s_full[i], 1); mbar_init(&sm.pts_full[i], 1); mbar_init(&sm.pv_done[i], 1);
+            mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
@@ -228,7 +232,10 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
                 TC_TRACE(j, 0);
                 mbar_arrive_expect_tx(&sm.k_full, TC_TILE_BYTES);
                 bulk_tile(sm.k, Kw + (tile0 + j) * TC_TILE_BYTES, &sm.k_full);
-                if (j >= 2) mbar_wait(&sm.p_full[buf], ((j - 2) >> 1) & 1);   // softmax(j-2) is done with pts[buf]
+                if (j >= 2) {                                            // softmax(j-2) is done with pts[buf]
+                    mbar_wait(&sm.p_full[buf][0], ((j - 2) >> 1) & 1);
+                    mbar_wait(&sm.p_full[buf][1], ((j - 2) >> 1) & 1);
+                }
                 mbar_arrive_expect_tx(&sm.pts_full[buf], TC_PTS_BYTES);
                 bulk_g2s(sm.pts[buf], Pw + (tile0 + j) * TC_PTS_FLOATS, TC_PTS_BYTES, &sm.pts_full[buf]);
             }
@@ -263,21 +270,22 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
                     umma_commit(&sm.s_full[buf ^ 1]);
                     umma_commit(&sm.k_empty);
                 }
-                mbar_wait(&sm.p_full[buf], (j >> 1) & 1);
                 mbar_wait(&sm.v_full, j & 1);
-                TC_TRACE(j, 3);
-                tc_fence_after();
-                issue_pv<128 / NWG>(tmem + TM_O, tmem + TM_S + (uint32_t)buf * 128u, v_addr, terms, j > 0 ? 1u : 0u);
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    mbar_wait(&sm.p_full[buf][g], (j >> 1) & 1);
+                    if (g == 0) TC_TRACE(j, 3);
+                    tc_fence_after();
+                    issue_pv_half(tmem + TM_O + (uint32_t)g * 128u, tmem + TM_S + (uint32_t)buf * 128u + (uint32_t)g * 64u,
+                                  v_addr + (uint32_t)g * TC_BLOCK_BYTES, terms, j > 0 ? 1u : 0u);
+                    umma_commit(&sm.pv_done[g]);
+                }
                 umma_commit(&sm.v_empty);
-                umma_commit(&sm.pv_done);
             }
         }
     } else {
         // ============================== softmax warpgroups ==============================
-        constexpr int KW = TC_BN / NWG;              // keys of a tile handled by one warpgroup
-        constexpr int NP = KW / 2;                   // ... as key pairs
-        constexpr int OW = TC_C / NWG;               // O columns a warpgroup rescales / writes out
-        const int wg = (warp - 3) >> 2;
+        const int wg = (warp - 3) >> 2;              // keys [64 wg, 64 wg + 64) of every tile
         const int quarter = warp & 3;                // TMEM lane quarter this warp may access
         const int row = quarter * 32 + lane;         // query row inside the CTA tile
         const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
@@ -286,27 +294,29 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
         const float2 qsx = make_float2(qp[0], qp[0]), qsy = make_float2(qp[2], qp[2]), qsz = make_float2(qp[4], qp[4]);
         const float2 qtx = make_float2(qp[6], qp[6]), qty = make_float2(qp[8], qp[8]), qtz = make_float2(qp[10], qp[10]);
         const float2 neg_inv2 = make_float2(-inv_sig2, -inv_sig2), one2 = make_float2(1.0f, 1.0f);
+        const uint32_t o_own = tmem + lane_base + TM_O + (uint32_t)wg * 128u;      // this warpgroup's accumulator
         float m = -INFINITY, l = 0.f;
+        const bool tr = threadIdx.x == 96;
 
         for (int j = 0; j < NT; ++j) {
             const int buf = j & 1;
             const uint32_t par = (j >> 1) & 1;
             mbar_wait(&sm.pts_full[buf], par);
             mbar_wait(&sm.s_full[buf], par);
-            if (threadIdx.x == 96) TC_TRACE(j, 4);
+            if (tr) TC_TRACE(j, 4);
             tc_fence_after();
-            const uint32_t s_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)(wg * KW);
+            const uint32_t s_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)wg * 64u;
             const int nvalid = N - j * TC_BN;        // keys of this tile that exist
-            float2 x[NP];
+            float2 x[32];                            // 64 keys as 32 pairs
             float tmax = -INFINITY;
 #pragma unroll
-            for (int h = 0; h < KW / 32; ++h) {
+            for (int h = 0; h < 2; ++h) {
                 uint32_t r[32];
                 tmem_ld32(s_col + h * 32, r);
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const int kp = wg * NP + h * 16 + i;     // key pair inside the tile
+                    const int kp = wg * 32 + h * 16 + i;     // key pair inside the tile
                     const float4 pa = sm.pts[buf][kp][0], pb = sm.pts[buf][kp][1], pc = sm.pts[buf][kp][2];
                     float2 dx = __fadd2_rn(qsx, make_float2(-pa.x, -pa.y));
                     float2 dy = __fadd2_rn(qsy, make_float2(-pa.z, -pa.w));
@@ -330,51 +340,47 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
             if (nvalid < TC_BN) {                    // last, partial tile: keys past N do not exist
                 tmax = -INFINITY;
 #pragma unroll
-                for (int i = 0; i < NP; ++i) {
-                    const int key = wg * KW + 2 * i;
+                for (int i = 0; i < 32; ++i) {
+                    const int key = wg * 64 + 2 * i;
                     if (key >= nvalid) x[i].x = -INFINITY;
                     if (key + 1 >= nvalid) x[i].y = -INFINITY;
                     tmax = fmaxf(tmax, fmaxf(x[i].x, x[i].y));
                 }
             }
-            if (threadIdx.x == 96) TC_TRACE(j, 5);
-            // tile row max across the warpgroups
-            sm.smax[buf][wg][row] = tmax;
-            named_bar_sync(1, NWG * 128);
-#pragma unroll
-            for (int g = 0; g < NWG; ++g) tmax = fmaxf(tmax, sm.smax[buf][g][row]);
-            // lazy rescale: keep the old reference max unless the row max grew by more than 2^8
-            if (j == 0) {
-                m = tmax;
-            } else {
-                // PV(j-1) has finished accumulating into O.  Waited for on every tile (normally already
-                // complete here) so that no waiter ever lags two phases behind the barrier.
-                mbar_wait(&sm.pv_done, (j - 1) & 1);
-                if (threadIdx.x == 96) TC_TRACE(j, 6);
+            if (tr) TC_TRACE(j, 5);
+            // Lazy rescale: keep the old reference max unless this warpgroup's row max grew by more
+            // than 2^8.  (m stays -inf while every key seen so far was past N: only warpgroup 1 of a
+            // one-tile problem; then p = exp2(-inf - (-inf)) must not be evaluated.)
+            if (j > 0) {
+                // PV_g(j-1) has finished accumulating into O_g.  Waited for on every tile (normally
+                // already complete) so that no waiter ever lags two phases behind the barrier.
+                mbar_wait(&sm.pv_done[wg], (j - 1) & 1);
+                if (tr) TC_TRACE(j, 6);
                 const bool need = tmax > m + TC_RESCALE_LOG2;
                 if (__any_sync(0xffffffffu, need)) {
                     tc_fence_after();
-                    const float f = need ? fast_exp2(m - tmax) : 1.0f;
+                    const float f = need ? fast_exp2(m - tmax) : 1.0f;   // m = -inf: f = 0, O_g was 0
                     if (need) { m = tmax; l *= f; }
-                    const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)(wg * OW);
 #pragma unroll
-                    for (int h = 0; h < OW / 32; ++h) {
+                    for (int h = 0; h < 4; ++h) {
                         uint32_t r[32];
-                        tmem_ld32(o_col + h * 32, r);
+                        tmem_ld32(o_own + h * 32, r);
                         tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
-                        tmem_st32(o_col + h * 32, r);
+                        tmem_st32(o_own + h * 32, r);
                     }
                     tmem_st_wait();
                 }
+            } else {
+                m = tmax;
             }
             // P = exp2(x - m), split into fp16 hi/lo, packed two keys per TMEM column
-            const uint32_t p_col = tmem + lane_base + TM_S + (uint32_t)buf * 128u + (uint32_t)(wg * KW);
+            const float m_use = (m == -INFINITY) ? 0.0f : m;             // all-masked rows: p = exp2(-inf) = 0
+            const float2 neg_m = make_float2(-m_use, -m_use);
             float2 psum = make_float2(0.f, 0.f);
-            const float2 neg_m = make_float2(-m, -m);
 #pragma unroll
-            for (int g = 0; g < NP / 16; ++g) {
+            for (int g = 0; g < 2; ++g) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
@@ -386,39 +392,48 @@ __global__ void __launch_bounds__(96 + NWG * 128, 1) attn_tc_kernel(const uint8_
                     const float2 rem = __fadd2_rn(p, make_float2(-back.x, -back.y));
                     lo[i] = pack_half2(rem.x, rem.y);
                 }
-                tmem_st16(p_col + g * 16, hi);
-                if (terms > 1) tmem_st16(p_col + NP + g * 16, lo);
+                tmem_st16(s_col + g * 16, hi);
+                if (terms > 1) tmem_st16(s_col + 32 + g * 16, lo);
             }
             l += psum.x + psum.y;
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.p_full[buf]);
-            if (threadIdx.x == 96) TC_TRACE(j, 7);
+            if (lane == 0) mbar_arrive(&sm.p_full[buf][wg]);
+            if (tr) TC_TRACE(j, 7);
         }
-        // ---- epilogue: msg = O / l ----
+        // ---- epilogue: combine the two warpgroups' partial softmaxes, msg = O / L ----
+        sm.mfin[wg][row] = m;
         sm.lsum[wg][row] = l;
-        mbar_wait(&sm.pv_done, (NT - 1) & 1);
+        mbar_wait(&sm.pv_done[0], (NT - 1) & 1);
+        mbar_wait(&sm.pv_done[1], (NT - 1) & 1);
         tc_fence_after();
-        named_bar_sync(1, NWG * 128);
-        float lt = 0.f;
-#pragma unroll
-        for (int g = 0; g < NWG; ++g) lt += sm.lsum[g][row];
-        const float inv_l = 1.0f / lt;
+        named_bar_sync(1, 256);
+        const float m0 = sm.mfin[0][row], m1 = sm.mfin[1][row];
+        const float M = fmaxf(m0, m1);
+        const float a0 = (m0 == -INFINITY) ? 0.f : fast_exp2(m0 - M), a1 = (m1 == -INFINITY) ? 0.f : fast_exp2(m1 - M);
+        const float inv_l = 1.0f / (sm.lsum[0][row] * a0 + sm.lsum[1][row] * a1);
+        const float c0 = a0 * inv_l, c1 = a1 * inv_l;
         const int grow = qt * TC_BM + row;
-        const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)(wg * OW);
-        float* orow = out + ((size_t)b * N + min(grow, N - 1)) * ld_out + wg * OW;
+        const uint32_t o_col = tmem + lane_base + TM_O + (uint32_t)wg * 64u;     // output channels [64 wg, +64)
+        float* orow = out + ((size_t)b * N + min(grow, N - 1)) * ld_out + wg * 64;
 #pragma unroll
-        for (int h = 0; h < OW / 32; ++h) {
-            uint32_t r[32];
-            tmem_ld32(o_col + h * 32, r);
+        for (int h = 0; h < 2; ++h) {
+            uint32_t r0[32], r1[32];
+            tmem_ld32(o_col + h * 32, r0);
+            tmem_ld32(o_col + 128 + h * 32, r1);
             tmem_ld_wait();
             if (grow < N) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 4)
-                    *reinterpret_cast<float4*>(orow + h * 32 + i) =
-                        make_float4(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l,
-                                    __uint_as_float(r[i + 2]) * inv_l, __uint_as_float(r[i + 3]) * inv_l);
+                for (int i = 0; i < 32; i += 4) {
+                    float4 o;
+                    // c_g = 0 when warpgroup g saw no valid key: its accumulator may hold anything
+                    o.x = (c0 != 0.f ? __uint_as_float(r0[i]) * c0 : 0.f) + (c1 != 0.f ? __uint_as_float(r1[i]) * c1 : 0.f);
+                    o.y = (c0 != 0.f ? __uint_as_float(r0[i + 1]) * c0 : 0.f) + (c1 != 0.f ? __uint_as_float(r1[i + 1]) * c1 : 0.f);
+                    o.z = (c0 != 0.f ? __uint_as_float(r0[i + 2]) * c0 : 0.f) + (c1 != 0.f ? __uint_as_float(r1[i + 2]) * c1 : 0.f);
+                    o.w = (c0 != 0.f ? __uint_as_float(r0[i + 3]) * c0 : 0.f) + (c1 != 0.f ? __uint_as_float(r1[i + 3]) * c1 : 0.f);
+                    *reinterpret_cast<float4*>(orow + h * 32 + i) = o;
+                }
             }
         }
     }
@@ -452,13 +467,11 @@ int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, c
     uint8_t* Kw = Qw + tiles * TC_TILE_BYTES;
     uint8_t* Vw = Kw + tiles * TC_TILE_BYTES;
     float* Pw = reinterpret_cast<float*>(Vw + tiles * TC_TILE_BYTES);
-    static int nwg = 0;
-    if (nwg == 0) {
-        const char* e = getenv("PDSC_ATTN_NWG");
-        nwg = (e && atoi(e) == 2) ? 2 : 4;
+    static bool attr_set = false;
+    if (!attr_set) {
         cudaFuncSetAttribute(attn_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
-        cudaFuncSetAttribute(attn_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
-        cudaFuncSetAttribute(attn_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
+        cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024);
+        attr_set = true;
     }
     const float qscale = 1.4426950408889634f / sqrtf((float)C);
     attn_prep_kernel<<<dim3(NT, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, NT, qscale, Qw, Kw, Vw, Pw);
@@ -467,10 +480,7 @@ int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, c
     long long* trace = nullptr;
     const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA (0,0)
     if (trace_path) { cudaMalloc(&trace, sizeof(long long) * 8 * NT); cudaMemset(trace, 0, sizeof(long long) * 8 * NT); }
-    if (nwg == 2)
-        attn_tc_kernel<2><<<dim3(NT, B), 96 + 2 * 128, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2, terms, trace);
-    else
-        attn_tc_kernel<4><<<dim3(NT, B), 96 + 4 * 128, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2, terms, trace);
+    attn_tc_kernel<<<dim3(NT, B), TC_THREADS, sizeof(TcSmem) + 1024, st>>>(Qw, Kw, Vw, Pw, out, ld_out, N, NT, inv_sig2, terms, trace);
     if (trace) {
         cudaStreamSynchronize(st);
         long long* h = (long long*)malloc(sizeof(long long) * 8 * NT);
