@@ -69,6 +69,15 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
                        int B, int N, int C, float sigma_spat, int mode,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Operand packing for the channel-last 1x1-conv GEMMs of NonLocalNet / NonLocalBlock
+ *  (models/PointDSC.py:12-23,54-62; the GEMMs themselves stay torch/cuBLAS calls).
+ *  v = x (+ add) (then ReLU if relu != 0), x/add/y_out fp32 [rows,K]; y_out (nullable) receives v;
+ *  out16 fp16 [rows,Kp] receives [hi(v) | hi(v) | lo(v) | 1 1 0...] with hi+lo the two-fp16 split
+ *  of v, so that out16 @ [W_hi; W_lo; W_hi; b_hi; b_lo; 0] (fp16 inputs, fp32 accumulate) = v W + b
+ *  at fp32-grade accuracy.  K % 8 == 0, Kp % 8 == 0, Kp >= 3K+2. */
+int pdsc_split16_rows(const float* x, const float* add, float* y_out, void* out16, int64_t rows, int K, int Kp,
+                      int relu, void* stream);
+
 /* (c) NMS seed picking; replaces PointDSC.pick_seeds models/PointDSC.py:199-217.
  *  is_local_max[i] = all_j (score_i >= score_j  or  |s_i-s_j| >= R);
  *  seeds = first S indices ordered by (score*is_local_max descending, index ascending).

@@ -39,6 +39,7 @@ SIGNATURES = {
                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_post_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
                                  c_void_p]),
+    "pdsc_split16_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                    c_void_p, c_void_p]),
     "pdsc_power_normalize": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -149,6 +150,25 @@ def nonlocal_attn(q, k, v, src, tgt, sigma_spat, mode=ATTN_FP32, out=None, ws=No
     _check(rc, "pdsc_nonlocal_attn")
     _count()
     return out
+
+
+def split_kp(K):
+    """Packed row length (fp16 elements) for K input channels: [hi|hi|lo|1 1 0..] rounded up to 8."""
+    return (3 * K + 2 + 7) // 8 * 8
+
+
+def split16_rows(x, add=None, relu=False, y_out=None, out16=None):
+    """x (+add), optional ReLU -> packed fp16 [rows, split_kp(K)]; y_out (may alias x) gets the fp32 value."""
+    lib = load()
+    rows, K = x.shape
+    Kp = split_kp(K)
+    if out16 is None:
+        out16 = torch.empty(rows, Kp, dtype=torch.float16, device=x.device)
+    rc = lib.pdsc_split16_rows(_ptr(x, torch.float32, "x"), _ptr(add, torch.float32, "add"), _ptr(y_out, torch.float32, "y_out"),
+                               _ptr(out16, torch.float16, "out16"), rows, K, Kp, 1 if relu else 0, _stream())
+    _check(rc, "pdsc_split16_rows")
+    _count()
+    return out16
 
 
 def pick_seeds(src, scores, R, S, ws=None, want_aux=False):

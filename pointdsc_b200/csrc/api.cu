@@ -145,6 +145,14 @@ int pdsc_post_refine(float* trans_inout, const float* src, const float* tgt, int
                               reinterpret_cast<cudaStream_t>(stream));
 }
 
+int pdsc_split16_rows(const float* x, const float* add, float* y_out, void* out16, int64_t rows, int K, int Kp, int relu,
+                      void* stream) {
+    PDSC_REQUIRE(x && out16, "split16_rows: null pointer");
+    PDSC_REQUIRE(rows > 0 && K > 0 && K % 8 == 0 && Kp % 8 == 0 && Kp >= 3 * K + 2, "split16_rows: need K %% 8 == 0, Kp %% 8 == 0, Kp >= 3K+2");
+    PDSC_REQUIRE(aligned16(x) && aligned16(out16) && (!add || aligned16(add)) && (!y_out || aligned16(y_out)), "split16_rows: pointers must be 16-byte aligned");
+    return launch_split16_rows(x, add, y_out, out16, rows, K, Kp, relu, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin, int row_end,
                        float sigma_spat, const int32_t* converged_flag, void* stream) {
     PDSC_REQUIRE(src && tgt && v && y, "compat_matvec: null pointer");

@@ -202,6 +202,8 @@ int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, c
                    size_t ws_bytes, cudaStream_t st);
 int launch_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin,
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st);
+int launch_split16_rows(const float* x, const float* add, float* y_out, void* out16, long long rows, int K, int Kp,
+                        int relu, cudaStream_t st);
 size_t power_workspace(int N);
 int power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
                     int32_t* iters_out, void* ws, size_t ws_bytes, cudaStream_t st);

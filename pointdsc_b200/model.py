@@ -68,6 +68,19 @@ class NonLocalNet(nn.Module):
             self.blocks[f"NonLocal_layer_{i}"] = NonLocalBlock(num_channels)
 
 
+def _pack_split(Wt, b):
+    """[K,out] fp32 weight (already transposed/folded) + bias -> fp16 [Kp,out] operand
+    [W_hi; W_lo; W_hi; b_hi; b_lo; 0] matching the row layout written by pdsc_split16_rows."""
+    K, out = Wt.shape
+    Kp = _cabi.split_kp(K)
+    hi = Wt.half()
+    lo = (Wt - hi.float()).half()
+    bh = b.half()
+    bl = (b - bh.float()).half()
+    pad = torch.zeros(Kp - 3 * K - 2, out, dtype=torch.float16, device=Wt.device)
+    return torch.cat([hi, lo, hi, bh[None], bl[None], pad], dim=0).contiguous()
+
+
 def _fold(conv: nn.Conv1d, bn: nn.BatchNorm1d | None):
     """Returns (W^T [in,out], b [out]) of a 1x1 conv with an eval-mode BatchNorm folded in."""
     W = conv.weight.detach()[:, :, 0].float()
@@ -101,6 +114,9 @@ class PointDSC(nn.Module):
                 nn.init.constant_(m.bias, 0)
         # kernel selection for the attention contraction (include/pointdsc_b200.h PDSC_ATTN_*)
         self.attn_mode = _MODE_NAMES[os.environ.get("POINTDSC_ATTN_MODE", "split16")]
+        # how the 1x1-conv GEMMs run: "split16" = fp16 hi/lo operands on the tensor cores (torch.mm with
+        # fp32 accumulation/output, fp32-grade accuracy), "fp32" = plain fp32 addmm
+        self.mlp_mode = os.environ.get("POINTDSC_MLP_MODE", "split16")
         self._packed = None
         self._ws = _cabi.Workspace()
 
@@ -133,13 +149,17 @@ class PointDSC(nn.Module):
             Wq, bq = _fold(nl.projection_q, None)
             Wk, bk = _fold(nl.projection_k, None)
             Wv, bv = _fold(nl.projection_v, None)
-            layers.append(dict(
+            L = dict(
                 pcn=_fold(pcn[0], pcn[1]),
                 qkv=(torch.cat([Wq, Wk, Wv], dim=1).contiguous(), torch.cat([bq, bk, bv]).contiguous()),
                 m0=_fold(nl.fc_message[0], nl.fc_message[1]),
                 m3=_fold(nl.fc_message[3], nl.fc_message[4]),
                 m6=_fold(nl.fc_message[6], None),
-            ))
+            )
+            if L["pcn"][0].is_cuda:
+                for name in ("pcn", "qkv", "m0", "m3", "m6"):
+                    L[name + "_s"] = _pack_split(*L[name])
+            layers.append(L)
         P["layers"] = layers
         P["cls"] = [_fold(self.classification[i], None) for i in (0, 2, 4)]
         # one host sync at pack time instead of one per forward
@@ -170,6 +190,8 @@ class PointDSC(nn.Module):
         C = self.num_channels
         W, b = P["layer0"]
         feat = torch.addmm(b, corr_pos.reshape(B * N, -1), W)
+        if self.mlp_mode == "split16" and feat.is_cuda and C % 16 == 0:
+            return self._encode_split16(P, feat, src, tgt, B, N, C)
         for L in P["layers"]:
             feat = torch.relu_(torch.addmm(L["pcn"][1], feat, L["pcn"][0]))
             qkv = torch.addmm(L["qkv"][1], feat, L["qkv"][0]).view(B, N, 3 * C)
@@ -179,6 +201,29 @@ class PointDSC(nn.Module):
             m = torch.relu_(torch.addmm(L["m3"][1], m, L["m3"][0]))
             feat = torch.addmm(feat, m, L["m6"][0]).add_(L["m6"][1])
         return feat.view(B, N, C)
+
+    def _encode_split16(self, P, feat, src, tgt, B, N, C):
+        """Same layer sequence with every GEMM on the tensor cores: activations are packed to fp16
+        hi/lo rows by pdsc_split16_rows (which also fuses the residual add and the ReLU) and
+        multiplied by the pre-packed weights with fp32 accumulation (torch.mm, out_dtype=float32)."""
+        f32 = torch.float32
+        resid = None                      # feat of the next layer = resid + m6 (added inside the next split)
+        x = feat
+        for L in P["layers"]:
+            xp = _cabi.split16_rows(x, add=resid)                                   # feat -> packed
+            y1 = torch.mm(xp, L["pcn_s"], out_dtype=f32)                            # PointCN conv+BN
+            xp = _cabi.split16_rows(y1, relu=True, y_out=y1)                        # ReLU (kept in y1 for the residual)
+            qkv = torch.mm(xp, L["qkv_s"], out_dtype=f32).view(B, N, 3 * C)
+            msg = _cabi.nonlocal_attn(qkv[:, :, 0:C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:3 * C], src, tgt,
+                                      P["sigma_spat"], mode=self.attn_mode, ws=self._ws)
+            xp = _cabi.split16_rows(msg.view(B * N, C))
+            m = torch.mm(xp, L["m0_s"], out_dtype=f32)
+            xp = _cabi.split16_rows(m, relu=True)
+            m = torch.mm(xp, L["m3_s"], out_dtype=f32)
+            xp = _cabi.split16_rows(m, relu=True)
+            x = torch.mm(xp, L["m6_s"], out_dtype=f32)                              # message MLP output
+            resid = y1
+        return (x + resid).view(B, N, C)
 
     def classify(self, feat):
         """corr_features [B,N,C] -> raw confidence logits [B,N] (:107-113,171)."""

@@ -9,7 +9,7 @@ TRANS_TOL = 1e-4        # translation <= 1e-4 m
 CONF_TOL = 1e-4         # confidences <= 1e-4 abs
 
 
-def golden_model(meta, device="cuda", attn_mode=None):
+def golden_model(meta, device="cuda", attn_mode=None, mlp_mode=None):
     from pointdsc_b200 import PointDSC
     fam = synth.CONFIGS[meta["family"]]
     sd = synth.make_state_dict(meta["weight_seed"], num_layers=meta["num_layers"], sigma_d=fam["sigma_d"])
@@ -18,6 +18,8 @@ def golden_model(meta, device="cuda", attn_mode=None):
     m = m.to(device)
     if attn_mode is not None:
         m.attn_mode = attn_mode
+    if mlp_mode is not None:
+        m.mlp_mode = mlp_mode
     return m, sd
 
 

@@ -9,19 +9,23 @@ from parity import CONF_TOL, assert_labels_match, assert_trans_close, golden_mod
 
 pytestmark = pytest.mark.gpu
 
-MODES = ["fp32", "split16"]
+# (attention precision mode, 1x1-conv GEMM mode)
+MODES = ["fp32", "split16", "split16+mlp16"]
 
 
 def _mode(name):
+    """-> kwargs for golden_model"""
     from pointdsc_b200 import _cabi
-    return {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16}[name]
+    return {"fp32": dict(attn_mode=_cabi.ATTN_FP32, mlp_mode="fp32"),
+            "split16": dict(attn_mode=_cabi.ATTN_SPLIT16, mlp_mode="fp32"),
+            "split16+mlp16": dict(attn_mode=_cabi.ATTN_SPLIT16, mlp_mode="split16")}[name]
 
 
 @pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_forward_vs_reference_golden(case, mode):
     meta, g = load_golden(case)
-    model, _ = golden_model(meta, attn_mode=_mode(mode))
+    model, _ = golden_model(meta, **_mode(mode))
     data = {k: g[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
     data["testing"] = True
     res = model(data)
@@ -70,7 +74,7 @@ def test_full_size_properties(fam, N, mode):
     meta = dict(family=fam, weight_seed=1234, num_layers=12,
                 ctor=dict(num_layers=12, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
                           nms_radius=cfg["nms_radius"]))
-    model, _ = golden_model(meta, attn_mode=_mode(mode))
+    model, _ = golden_model(meta, **_mode(mode))
     batch = synth.make_batch([0, 1] if fam == "3dmatch" else [100, 101], N, **cfg)
     data = {k: batch[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
     data["testing"] = True

@@ -317,3 +317,31 @@ def test_attention_split16_on_oracle_layers(case):
         worst = max(worst, float((msg.cpu() - ref).abs().max()) / max(1.0, float(ref.abs().max())))
     print(f"{case}: split16 attention worst relative-to-scale error over layers {worst:.3e}")
     assert worst < 5e-5
+
+
+# ------------------------------------------------------- operand packing for the 1x1-conv GEMMs
+@pytest.mark.parametrize("K,out", [(128, 384), (64, 64)])
+def test_split16_rows_gemm_matches_fp64(K, out):
+    from pointdsc_b200 import _cabi
+    from pointdsc_b200.model import _pack_split
+    g = torch.Generator().manual_seed(K)
+    rows = 3001
+    x = torch.randn(rows, K, generator=g) * 4
+    add = torch.randn(rows, K, generator=g)
+    Wt = torch.randn(K, out, generator=g) * 0.2
+    b = torch.randn(out, generator=g)
+    y_out = torch.empty(rows, K, device="cuda")
+    xp = _cabi.split16_rows(cu(x), add=cu(add), relu=True, y_out=y_out)
+    v = torch.relu(x + add)
+    assert torch.equal(y_out.cpu(), v)
+    Kp = _cabi.split_kp(K)
+    assert xp.shape == (rows, Kp)
+    hi = xp[:, :K].float().cpu()
+    assert torch.equal(hi, v.half().float()) and torch.equal(xp[:, K:2 * K].cpu(), xp[:, :K].cpu())
+    assert (hi + xp[:, 2 * K:3 * K].float().cpu() - v).abs().max() <= 2.0 ** -21 * v.abs().max()
+    assert torch.equal(xp[:, 3 * K:].float().cpu(), torch.tensor([1.0, 1.0] + [0.0] * (Kp - 3 * K - 2)).expand(rows, -1))
+    y = torch.mm(xp, _pack_split(cu(Wt), cu(b)), out_dtype=torch.float32).cpu()
+    ref = (v.double() @ Wt.double() + b.double())
+    err = (y.double() - ref).abs().max().item()
+    print(f"split16 GEMM K={K}: max abs err {err:.3e} (fp32 addmm: {((v @ Wt + b).double() - ref).abs().max().item():.3e})")
+    assert err < 2e-6 * ref.abs().max().item()
