@@ -1,0 +1,10 @@
+#!/bin/bash
+# Attention-kernel iteration on the GPU box: its parity tests, then timing of the kernel alone.
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -x -k "attention" --timeout=300 > gpurun_out/pytest_attn.log 2>&1
+echo "pytest exit $?"; tail -15 gpurun_out/pytest_attn.log
+for nwg in ${NWGS:-4 2}; do
+  echo "== NWG=$nwg"
+  PDSC_ATTN_NWG=$nwg timeout 120 python scripts/prof_attn.py split16 16 5000 10
+  PDSC_ATTN_NWG=$nwg timeout 120 python scripts/prof_attn.py fp16 16 5000 10
+done
