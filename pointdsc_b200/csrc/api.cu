@@ -2,6 +2,8 @@
 // workspace sizing.  No torch types cross this boundary.
 #include "common.cuh"
 
+#include <stdlib.h>
+
 #include <atomic>
 #include <stdarg.h>
 #include <string.h>
@@ -69,7 +71,11 @@ int pdsc_check_device(void) {
 
 size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode) {
     switch (op) {
-        case PDSC_OP_NONLOCAL_ATTN: return attn_workspace(B, N, C, mode);
+        case PDSC_OP_NONLOCAL_ATTN: {
+            if (mode == PDSC_ATTN_FP32) return 0;
+            const size_t a = attn_workspace(B, N, C, mode), b = attn_pp_workspace(B, N);
+            return a > b ? a : b;
+        }
         case PDSC_OP_PICK_SEEDS: return pick_seeds_workspace(B, N);
         case PDSC_OP_SEED_KNN: return seed_knn_workspace(B, N, S);
         case PDSC_OP_SEED_HYPOTHESES: return seed_hypotheses_workspace(B, S, k, 31);
@@ -90,8 +96,13 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
     PDSC_REQUIRE(sigma_spat > 0.f, "nonlocal_attn: sigma_spat must be positive");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (mode == PDSC_ATTN_FP32) return launch_attn_fp32(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, st);
-    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16)
+    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16) {
+        static int impl = -1;                       // PDSC_ATTN_IMPL=tc selects the previous single-tile kernel
+        if (impl < 0) { const char* e = getenv("PDSC_ATTN_IMPL"); impl = (e && e[0] == 't') ? 1 : 0; }
+        if (impl == 0)
+            return launch_attn_pp(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
         return launch_attn_tc(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
+    }
     set_error("nonlocal_attn: unknown precision mode %d", mode);
     return PDSC_ERR_ARG;
 }

@@ -1,0 +1,828 @@
+// (a) Compatibility-weighted non-local attention on the 5th-generation tensor cores, ping-pong form.
+// Replaces models/PointDSC.py:150-153 + NonLocalBlock.forward :39-42.
+//
+//   S = Q K^T / sqrt(C)            tcgen05.mma kind::f16, fp32 accumulators in TMEM
+//   W = softmax_j(compat_ij S_ij)  CUDA cores: compat recomputed from 6 floats per correspondence
+//                                  (never stored), online softmax with a lazily raised reference max
+//   msg = W V                      tcgen05.mma with P read from TMEM (aliasing S) and V^T from smem
+//
+// Precision (PDSC_ATTN_SPLIT16): every fp32 operand x is split into fp16 hi + fp16 lo (22 mantissa
+// bits) and each contraction is issued as hi*hi + hi*lo + lo*hi with fp32 accumulation.
+// PDSC_ATTN_FP16 issues only hi*hi.
+//
+// One CTA works on 256 query rows of one pair as two 128-row sub-tiles X = A, B that alternate on
+// the tensor pipe (while the CUDA cores do the softmax of one, the tensor cores do the MMAs of the
+// other), looping over 64-key tiles:
+//   warps 0..15  softmax: warp w -> TMEM lane quarter w%4, sub-tile X = w/8, 16-lane half (w/4)%2.
+//                Two threads per query row (lane l and l+16 of one warp, tcgen05 .16x32bx2 shape)
+//                take 32 keys each, so the row maximum / sum exchange is one warp shuffle and no
+//                warp ever waits for another warp inside a tile.
+//   warp 16      producer: bulk-async (TMA engine) copies of K, V^T, key-point and Q_lo tiles
+//   warp 17      MMA issuer (one elected lane), owns the TMEM allocation
+// TMEM columns: S_A [0,64) S_B [64,128) O_A [128,256) O_B [256,384) Qhi_A [384,448) Qhi_B [448,512).
+// P overwrites S in place as fp16 pairs (hi: columns 0..31, lo: 32..63 of the S block).
+#include "common.cuh"
+#include "sm100.cuh"
+
+#include <math.h>
+#include <stdlib.h>
+
+namespace pdsc {
+
+using namespace sm100;
+
+constexpr int PP_C = 128;                 // channels (head dim)
+constexpr int PP_SUB = 128;               // rows per sub-tile
+constexpr int PP_BM = 2 * PP_SUB;         // query rows per CTA
+constexpr int PP_BN = 64;                 // keys per tile
+constexpr uint32_t PP_QTILE_BYTES = 65536;   // per 128 rows: hi row-linear [128][64 words] | lo 2 swizzled blocks [128 rows x 128 B]
+constexpr uint32_t PP_QLO_OFF = 32768;
+constexpr uint32_t PP_QLO_BYTES = 32768;
+constexpr uint32_t PP_KTILE_BYTES = 32768;   // per 64 keys: hi blk(ch 0-63) | hi blk(ch 64-127) | lo blk | lo blk, 8 KB each
+constexpr uint32_t PP_KBLK_BYTES = 8192;
+constexpr uint32_t PP_VTILE_BYTES = 32768;   // per 64 keys: hi [128 ch rows x 64 keys] | lo, 16 KB each
+constexpr uint32_t PP_VHALF_BYTES = 16384;
+// key points per key PAIR: sx0 sx1 sy0 sy1 sz0 sz1 tx0 tx1 ty0 ty1 tz0 tz1 (48 B); pairs 16..31 sit 16 B further so
+// that the two half-warps (which read pairs i and 16 + i in one LDS.128) hit different banks
+constexpr uint32_t PP_PTS_FLOATS = (PP_BN / 2) * 12 + 4;
+constexpr uint32_t PP_PTS_BYTES = PP_PTS_FLOATS * 4;
+constexpr float PP_RESCALE_LOG2 = 8.0f;      // lazy rescale threshold (log2 units)
+constexpr uint32_t PT_S = 0, PT_O = 128, PT_Q = 384;
+constexpr int PP_SOFT_WARPS = 16;
+constexpr int PP_THREADS = (PP_SOFT_WARPS + 4) * 32;   // + one warpgroup of role warps (producer, MMA issuer, 2 idle)
+
+struct PpSmem {
+    uint8_t qlo[2][PP_QLO_BYTES];
+    uint8_t k[2][PP_KTILE_BYTES];
+    uint8_t v[2][PP_VTILE_BYTES];
+    float4 pts[2][PP_PTS_FLOATS / 4 + 3];     // (+3: stages stay 64-byte aligned)
+    uint64_t q_full[2], q_free;
+    uint64_t k_full[2], k_empty[2], v_full[2], v_empty[2], pts_full[2], pts_empty[2];
+    uint64_t s_full[2], p_full[2], pv_done[2];
+    uint32_t tmem_base;
+};
+
+// byte offset of (row r, 16-byte chunk c) inside a block of 128-byte rows with the 128B swizzle
+__host__ __device__ inline uint32_t pp_swz(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
+
+__device__ __forceinline__ void pp_split8(const float (&x)[8], uint4& hi, uint4& lo) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        h[i] = pack_half2(x[2 * i], x[2 * i + 1]);
+        float2 back = unpack_half2(h[i]);
+        l[i] = pack_half2(x[2 * i] - back.x, x[2 * i + 1] - back.y);
+    }
+    hi = make_uint4(h[0], h[1], h[2], h[3]);
+    lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Prep: fp32 q,k,v [B,N,C] -> fp16 hi/lo tiles.  K, V^T and Q_lo tiles are written as the exact
+// shared-memory image the MMAs read (so a tile is ONE contiguous bulk copy; V transposed so that
+// keys become the contraction dim).  Q_hi is row-linear (it goes to TMEM through registers).
+// q is pre-multiplied by log2(e)/sqrt(C); the key points are divided by sigma_d, so that
+// compat = sat(1 - (|ds| - |dt|)^2), and packed per key pair.  One CTA per 128 rows.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) attn_pp_prep_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                           const float* __restrict__ v, int64_t ld,
+                                                           const float* __restrict__ src, const float* __restrict__ tgt,
+                                                           int N, int NT128, float qscale, float inv_sigma,
+                                                           uint8_t* __restrict__ Qw, uint8_t* __restrict__ Kw,
+                                                           uint8_t* __restrict__ Vw, float* __restrict__ Pw) {
+    extern __shared__ __align__(16) float vt[];   // [128 keys][129] staging for the V transpose
+    const int t = blockIdx.x, b = blockIdx.y;
+    const int n0 = t * PP_SUB;
+    const size_t tile = (size_t)b * NT128 + t;
+    uint8_t* qd = Qw + tile * PP_QTILE_BYTES;
+    uint8_t* kd = Kw + tile * 2 * PP_KTILE_BYTES;   // two 64-key tiles
+    uint8_t* vd = Vw + tile * 2 * PP_VTILE_BYTES;
+    // Q and K: thread task = (row r, 8 consecutive channels)
+    for (int task = threadIdx.x; task < 128 * 16; task += 256) {
+        const int r = task >> 4, c8 = task & 15;
+        const int n = n0 + r;
+        float xq[8] = {0, 0, 0, 0, 0, 0, 0, 0}, xk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (n < N) {
+            const float4* pq = reinterpret_cast<const float4*>(q + ((size_t)b * N + n) * ld + c8 * 8);
+            const float4* pk = reinterpret_cast<const float4*>(k + ((size_t)b * N + n) * ld + c8 * 8);
+            float4 a0 = pq[0], a1 = pq[1], b0 = pk[0], b1 = pk[1];
+            xq[0] = a0.x * qscale; xq[1] = a0.y * qscale; xq[2] = a0.z * qscale; xq[3] = a0.w * qscale;
+            xq[4] = a1.x * qscale; xq[5] = a1.y * qscale; xq[6] = a1.z * qscale; xq[7] = a1.w * qscale;
+            xk[0] = b0.x; xk[1] = b0.y; xk[2] = b0.z; xk[3] = b0.w; xk[4] = b1.x; xk[5] = b1.y; xk[6] = b1.z; xk[7] = b1.w;
+        }
+        uint4 hi, lo;
+        pp_split8(xq, hi, lo);
+        *reinterpret_cast<uint4*>(qd + r * 256 + c8 * 16) = hi;
+        *reinterpret_cast<uint4*>(qd + PP_QLO_OFF + (uint32_t)(c8 >> 3) * 16384u + pp_swz(r, c8 & 7)) = lo;
+        pp_split8(xk, hi, lo);
+        uint8_t* kt = kd + (size_t)(r >> 6) * PP_KTILE_BYTES + (uint32_t)(c8 >> 3) * PP_KBLK_BYTES + pp_swz(r & 63, c8 & 7);
+        *reinterpret_cast<uint4*>(kt) = hi;
+        *reinterpret_cast<uint4*>(kt + 2 * PP_KBLK_BYTES) = lo;
+    }
+    // V^T: stage the [key][channel] tile, then thread task = (channel row, 8 consecutive keys)
+    for (int task = threadIdx.x; task < 128 * 32; task += 256) {
+        const int r = task >> 5, c4 = task & 31;
+        const int n = n0 + r;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (n < N) x = *reinterpret_cast<const float4*>(v + ((size_t)b * N + n) * ld + c4 * 4);
+        float* d = vt + r * 129 + c4 * 4;
+        d[0] = x.x; d[1] = x.y; d[2] = x.z; d[3] = x.w;
+    }
+    __syncthreads();
+    for (int task = threadIdx.x; task < 128 * 16; task += 256) {
+        const int ch = task & 127, k8 = task >> 7;   // lanes vary over channels: conflict-free smem reads
+        float x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = vt[(k8 * 8 + i) * 129 + ch];
+        uint4 hi, lo;
+        pp_split8(x, hi, lo);
+        uint8_t* vtile = vd + (size_t)(k8 >> 3) * PP_VTILE_BYTES + pp_swz(ch, k8 & 7);
+        *reinterpret_cast<uint4*>(vtile) = hi;
+        *reinterpret_cast<uint4*>(vtile + PP_VHALF_BYTES) = lo;
+    }
+    if (threadIdx.x < PP_SUB) {
+        // packed-pair SoA layout so the softmax loop can use FADD2/FFMA2 on two keys at once
+        const int n = min(n0 + (int)threadIdx.x, N - 1);
+        const float* s = src + ((size_t)b * N + n) * 3;
+        const float* g = tgt + ((size_t)b * N + n) * 3;
+        const int pr = (threadIdx.x & 63) >> 1;
+        float* d = Pw + (tile * 2 + (threadIdx.x >> 6)) * PP_PTS_FLOATS + pr * 12 + (pr >= 16 ? 4 : 0) + (threadIdx.x & 1);
+        d[0] = s[0] * inv_sigma; d[2] = s[1] * inv_sigma; d[4] = s[2] * inv_sigma;
+        d[6] = g[0] * inv_sigma; d[8] = g[1] * inv_sigma; d[10] = g[2] * inv_sigma;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// TMEM <-> registers with the .16x32bx2 shape: the warp touches 16 TMEM lanes starting at the lane
+// of `taddr`; thread t holds lane (t & 15), columns [col + (t >> 4) * SPLIT, ... + count).
+// (layout verified on hardware by scripts/micro/tmem_shapes.cu)
+// ------------------------------------------------------------------------------------------------
+template <int SPLIT>
+__device__ __forceinline__ void tmem_ld_h32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x32bx2.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32], %33;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr), "n"(SPLIT)
+        : "memory");
+}
+template <int SPLIT>
+__device__ __forceinline__ void tmem_st_h32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.16x32bx2.x32.b32 [%0], %33, "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]), "n"(SPLIT)
+        : "memory");
+}
+template <int SPLIT>
+__device__ __forceinline__ void tmem_st_h16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.16x32bx2.x16.b32 [%0], %17, "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "n"(SPLIT)
+        : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// MMA issue helpers (one thread).  Shared-memory operands are K-major 128B-swizzled blocks; a
+// 16-element k step advances the start address by 32 bytes inside the 128-byte row.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t pp_desc_add(uint64_t desc, uint32_t byte_off) { return desc + (uint64_t)(byte_off >> 4); }
+// Broadcast from lane 0: tells the compiler the value is warp-uniform (uniform registers, no per-MMA R2UR loop).
+__device__ __forceinline__ uint64_t pp_uniform64(uint64_t v) {
+    const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)v, 0), hi = __shfl_sync(0xffffffffu, (uint32_t)(v >> 32), 0);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+// One asm statement issues a whole run of MMAs (one hi/lo term of a contraction) with a single elect.sync,
+// TMEM addresses as immediates and the descriptors advanced inside the asm, so ptxas sees one straight-line
+// block with warp-uniform operands.  Every lane executes the statement; the elected lane issues.
+#define PP_TS "@pe tcgen05.mma.cta_group::1.kind::f16 [td], [ta], db, idc, pt;\n\t"
+#define PP_SS "@pe tcgen05.mma.cta_group::1.kind::f16 [td], da, db, idc, pt;\n\t"
+#define PP_ADV_TS(boff) "add.u32 ta, ta, 8;\n\tadd.s64 db, db, " #boff ";\n\t"
+#define PP_ADV_SS(aoff, boff) "add.s64 da, da, " #aoff ";\n\tadd.s64 db, db, " #boff ";\n\t"
+#define PP_HEAD                                                                      \
+    "{\n\t.reg .pred pe, p0, pt;\n\t.reg .b64 da, db;\n\t.reg .b32 ta, td, idc;\n\t" \
+    "elect.sync _|pe, 0xffffffff;\n\t"                                               \
+    "setp.ne.b32 p0, %1, 0;\n\t"                                                     \
+    "setp.eq.b32 pt, 0, 0;\n\t"                                                      \
+    "mov.b32 td, %2;\n\tmov.b32 idc, %3;\n\tmov.b64 db, %0;\n\t"
+
+// 8 k-steps, A from TMEM columns A0 + 8 kk, B = 64-row blocks of 8 KB (k-steps 0..3 in block 0, 4..7 in block 1)
+template <uint32_t D, uint32_t A0>
+__device__ __forceinline__ void pp_qk_run_ts(uint64_t k_desc, uint32_t acc_first) {
+    asm volatile(PP_HEAD "mov.b32 ta, %4;\n\t"
+                 "@pe tcgen05.mma.cta_group::1.kind::f16 [td], [ta], db, idc, p0;\n\t"
+                 PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS
+                 PP_ADV_TS(506) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS "}"
+                 ::"l"(k_desc), "r"(acc_first), "n"(D), "n"(umma_idesc_f16(128, 64)), "n"(A0)
+                 : "memory");
+}
+// same with A from shared memory (Q_lo: 128-row blocks of 16 KB)
+template <uint32_t D>
+__device__ __forceinline__ void pp_qk_run_ss(uint64_t q_desc, uint64_t k_desc) {
+    asm volatile(PP_HEAD "mov.b64 da, %4;\n\t"
+                 PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS
+                 PP_ADV_SS(1018, 506) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS "}"
+                 ::"l"(k_desc), "r"(1u), "n"(D), "n"(umma_idesc_f16(128, 64)), "l"(q_desc)
+                 : "memory");
+}
+// 4 k-steps, A = P from TMEM columns A0 + 8 kk, B = one 128-row block (V^T half)
+template <uint32_t D, uint32_t A0>
+__device__ __forceinline__ void pp_pv_run(uint64_t v_desc, uint32_t acc_first) {
+    asm volatile(PP_HEAD "mov.b32 ta, %4;\n\t"
+                 "@pe tcgen05.mma.cta_group::1.kind::f16 [td], [ta], db, idc, p0;\n\t"
+                 PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS "}"
+                 ::"l"(v_desc), "r"(acc_first), "n"(D), "n"(umma_idesc_f16(128, 128)), "n"(A0)
+                 : "memory");
+}
+
+// S_X[128 x 64 keys] = Q K^T.  terms = 3: Qhi Khi + Qhi Klo + Qlo Khi; 1: Qhi Khi.
+template <int X>
+__device__ __forceinline__ void pp_issue_qk(uint64_t qlo_desc, uint64_t k_desc, int terms) {
+    if (terms <= 0) return;
+    pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(k_desc, 0u);
+    if (terms > 1) {
+        pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), 1u);
+        pp_qk_run_ss<PT_S + 64u * X>(qlo_desc, k_desc);
+    }
+}
+// O_X[128 x 128 ch] (+)= P[128 x 64 keys] V.  terms = 3: Phi Vhi + Phi Vlo + Plo Vhi; 2: Phi Vhi + Phi Vlo; 1: Phi Vhi.
+template <int X>
+__device__ __forceinline__ void pp_issue_pv(uint64_t v_desc, int terms, uint32_t acc) {
+    if (terms <= 0) return;
+    pp_pv_run<PT_O + 128u * X, PT_S + 64u * X>(v_desc, acc);
+    if (terms > 1) pp_pv_run<PT_O + 128u * X, PT_S + 64u * X>(pp_desc_add(v_desc, PP_VHALF_BYTES), 1u);
+    if (terms > 2) pp_pv_run<PT_O + 128u * X, PT_S + 64u * X + 32u>(v_desc, 1u);
+}
+
+__device__ __forceinline__ float pp_fma_sat(float a, float b, float c) {
+    float d;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// compat of this thread's query point against NP key pairs -> w[NP] (two keys per float2)
+template <int NP>
+__device__ __forceinline__ void pp_compat_pairs(const float4* pts, const float2 (&qp)[6], float2 (&w)[NP]) {
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        const float4 pa = pts[3 * i], pb = pts[3 * i + 1], pc = pts[3 * i + 2];
+        float2 dx = __fadd2_rn(qp[0], make_float2(-pa.x, -pa.y));
+        float2 dy = __fadd2_rn(qp[1], make_float2(-pa.z, -pa.w));
+        float2 dz = __fadd2_rn(qp[2], make_float2(-pb.x, -pb.y));
+        float2 a2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+        const float2 ds = make_float2(fast_sqrt(a2.x), fast_sqrt(a2.y));
+        dx = __fadd2_rn(qp[3], make_float2(-pb.z, -pb.w));
+        dy = __fadd2_rn(qp[4], make_float2(-pc.x, -pc.y));
+        dz = __fadd2_rn(qp[5], make_float2(-pc.z, -pc.w));
+        a2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+        const float2 dt = make_float2(fast_sqrt(a2.x), fast_sqrt(a2.y));
+        const float2 c = __fadd2_rn(ds, make_float2(-dt.x, -dt.y));
+        w[i] = make_float2(pp_fma_sat(-c.x, c.x, 1.0f), pp_fma_sat(-c.y, c.y, 1.0f));   // max(0, 1 - c^2)
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Work decomposition ("stream-K"): the (pair, 256-row block, 64-key tile) steps are linearised and
+// cut into `gridDim.x` equal contiguous ranges, so every SM gets the same number of steps whatever
+// B and N are.  A range is walked as segments = (block, key tiles [j0,j1)).  A segment covering all
+// key tiles of its block writes the message directly; otherwise the CTA stores its un-normalised
+// partial (O, m, l) and the LAST contributor of that block (atomic counter) combines them.
+// A CTA has at most two partial segments (its first and its last) -> two slots per CTA.
+// ------------------------------------------------------------------------------------------------
+struct PpParams {
+    const uint8_t* Qw; const uint8_t* Kw; const uint8_t* Vw; const float* Pw;
+    float* out; int64_t ld_out;
+    float* part_o;          // [grid][2 slots][2 sub-tiles][128 rows][128 ch]
+    float* part_ml;         // [grid][2][2][128][2]  (m, l)
+    int* counters;          // [B * NRB][2]
+    int N, NRB, NT;         // rows, 256-row blocks per pair, 64-key tiles per pair
+    long long total_steps;  // B * NRB * NT
+    int qk_terms, pv_terms, dbg;   // hi/lo product terms issued per contraction
+    long long* trace;       // optional timeline of CTA 0 (PDSC_ATTN_TRACE): trace[step * 16 + event] = SM clock
+};
+
+struct PpSeg { int blk, j0, j1; };
+#define PP_TRACE(step, ev) do { if (tracing && (step) < 256) p.trace[(step) * 16 + (ev)] = clock64(); } while (0)
+
+__device__ __forceinline__ long long pp_range_lo(long long total, int c, int G) { return total * c / G; }
+
+// si-th segment of the range [lo, hi); returns false past the end.  `pos` carries the walk state.
+__device__ __forceinline__ bool pp_next_segment(long long& pos, long long hi, int NT, PpSeg& s) {
+    if (pos >= hi) return false;
+    s.blk = (int)(pos / NT);
+    s.j0 = (int)(pos - (long long)s.blk * NT);
+    const long long left = hi - pos;
+    s.j1 = (left < (long long)(NT - s.j0)) ? s.j0 + (int)left : NT;
+    pos += s.j1 - s.j0;
+    return true;
+}
+
+__device__ __forceinline__ float pp_ldcg(const float* p) {
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float4 pp_ldcg4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Main kernel.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p) {
+    constexpr int NP = 16;                   // key pairs per thread per tile (32 keys)
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // the 128B swizzle is anchored at 1024-byte boundaries of the shared window
+    PpSmem& sm = *reinterpret_cast<PpSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+    __shared__ int last_flag[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int G = gridDim.x, cta = blockIdx.x;
+    const int NT = p.NT;
+    const long long lo = pp_range_lo(p.total_steps, cta, G), hi = pp_range_lo(p.total_steps, cta + 1, G);
+    const bool tracing = p.trace != nullptr && cta == 0 && lane == 0;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&sm.q_full[i], PP_SOFT_WARPS / 2 + 1);
+            mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], 1);
+            mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], 1);
+            mbar_init(&sm.pts_full[i], 1); mbar_init(&sm.pts_empty[i], PP_SOFT_WARPS);
+            mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], PP_SOFT_WARPS / 2); mbar_init(&sm.pv_done[i], 1);
+        }
+        mbar_init(&sm.q_free, 1);
+        fence_barrier_init();
+    }
+    if (warp == PP_SOFT_WARPS + 1) tmem_alloc(&sm.tmem_base, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    // The allocation is the whole 512-column TMEM of the SM (one CTA per SM), so its base is column 0, lane 0:
+    // every TMEM address below is a compile-time constant.
+    if (sm.tmem_base != 0u) __trap();
+    constexpr uint32_t tmem = 0u;
+
+    if (warp >= PP_SOFT_WARPS) {
+        // role warpgroup: give registers back to the softmax warpgroups
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
+    }
+    if (warp == PP_SOFT_WARPS) {
+        // ============================== producer ==============================
+        if (lane == 0) {
+            long long pos = lo;
+            PpSeg s;
+            uint32_t kt = 0;
+            for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
+                const int b = s.blk / p.NRB, rb = s.blk - b * p.NRB;
+                const size_t q128 = (size_t)b * (2 * p.NRB) + 2 * rb;      // first 128-row tile of the block
+                const size_t kt0 = (size_t)b * (4 * p.NRB);                // first 64-key tile of the pair
+                if (si > 0) mbar_wait_role(&sm.q_free, (si - 1) & 1);      // all MMAs of the previous segment are done
+                for (int x = 0; x < 2; ++x) {
+                    mbar_arrive_expect_tx(&sm.q_full[x], PP_QLO_BYTES);
+                    bulk_g2s(sm.qlo[x], p.Qw + (q128 + x) * PP_QTILE_BYTES + PP_QLO_OFF, PP_QLO_BYTES, &sm.q_full[x]);
+                }
+                for (int j = s.j0; j < s.j1; ++j, ++kt) {
+                    const int st = kt & 1;
+                    const uint32_t par = ((kt >> 1) - 1) & 1;               // previous use of this stage
+                    if (kt >= 2) mbar_wait_role(&sm.k_empty[st], par);
+                    mbar_arrive_expect_tx(&sm.k_full[st], PP_KTILE_BYTES);
+                    bulk_g2s(sm.k[st], p.Kw + (kt0 + j) * PP_KTILE_BYTES, PP_KTILE_BYTES, &sm.k_full[st]);
+                    PP_TRACE(kt, 0);
+                    if (kt >= 2) mbar_wait_role(&sm.pts_empty[st], par);
+                    mbar_arrive_expect_tx(&sm.pts_full[st], PP_PTS_BYTES);
+                    bulk_g2s(sm.pts[st], p.Pw + (kt0 + j) * PP_PTS_FLOATS, PP_PTS_BYTES, &sm.pts_full[st]);
+                    if (kt >= 2) mbar_wait_role(&sm.v_empty[st], par);
+                    mbar_arrive_expect_tx(&sm.v_full[st], PP_VTILE_BYTES);
+                    bulk_g2s(sm.v[st], p.Vw + (kt0 + j) * PP_VTILE_BYTES, PP_VTILE_BYTES, &sm.v_full[st]);
+                    PP_TRACE(kt, 1);
+                }
+            }
+        }
+    } else if (warp == PP_SOFT_WARPS + 1) {
+        // ============================== MMA issuer ==============================
+        // The whole warp runs this loop (warp-uniform control flow keeps the descriptors in uniform
+        // registers); only the tcgen05 instructions themselves are predicated on an elected lane.
+        const uint64_t k_desc[2] = {umma_desc_sw128_kmajor(smem_u32(sm.k[0])), umma_desc_sw128_kmajor(smem_u32(sm.k[1]))};
+        const uint64_t v_desc[2] = {umma_desc_sw128_kmajor(smem_u32(sm.v[0])), umma_desc_sw128_kmajor(smem_u32(sm.v[1]))};
+        const uint64_t q_desc0 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[0])));
+        const uint64_t q_desc1 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[1])));
+        const int qk_terms = p.qk_terms, pv_terms = p.pv_terms;
+        long long pos = lo;
+        PpSeg s;
+        uint32_t kt = 0;
+        for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
+            const int n = s.j1 - s.j0;
+            // S_A(0), S_B(0)
+            mbar_wait_uniform(&sm.k_full[kt & 1], (kt >> 1) & 1);
+            {
+                const uint64_t kd = pp_uniform64(k_desc[kt & 1]);
+                mbar_wait_uniform(&sm.q_full[0], si & 1);
+                tc_fence_after();
+                pp_issue_qk<0>(q_desc0, kd, qk_terms);
+                umma_commit_elect(&sm.s_full[0]);
+                mbar_wait_uniform(&sm.q_full[1], si & 1);
+                tc_fence_after();
+                pp_issue_qk<1>(q_desc1, kd, qk_terms);
+                umma_commit_elect(&sm.s_full[1]);
+                umma_commit_elect(&sm.k_empty[kt & 1]);
+            }
+            for (int t = 0; t < n; ++t, ++kt) {
+                const int st = kt & 1, nx = st ^ 1;
+                const bool more = t + 1 < n;
+                const uint64_t vd = pp_uniform64(v_desc[st]), kd = pp_uniform64(k_desc[nx]);
+                const uint32_t acc = t > 0 ? 1u : 0u;
+                // ---- sub-tile A ----
+                mbar_wait_uniform(&sm.p_full[0], kt & 1);
+                PP_TRACE(kt, 2);
+                mbar_wait_uniform(&sm.v_full[st], (kt >> 1) & 1);
+                PP_TRACE(kt, 12);
+                tc_fence_after();
+                pp_issue_pv<0>(vd, pv_terms, acc);
+                umma_commit_elect(&sm.pv_done[0]);
+                if (more) {
+                    mbar_wait_uniform(&sm.k_full[nx], ((kt + 1) >> 1) & 1);
+                    tc_fence_after();
+                    PP_TRACE(kt, 13);
+                    pp_issue_qk<0>(q_desc0, kd, qk_terms);
+                    umma_commit_elect(&sm.s_full[0]);
+                }
+                PP_TRACE(kt, 4);
+                // ---- sub-tile B ----
+                mbar_wait_uniform(&sm.p_full[1], kt & 1);
+                PP_TRACE(kt, 3);
+                tc_fence_after();
+                pp_issue_pv<1>(vd, pv_terms, acc);
+                umma_commit_elect(&sm.pv_done[1]);
+                umma_commit_elect(&sm.v_empty[st]);
+                if (more) {
+                    pp_issue_qk<1>(q_desc1, kd, qk_terms);
+                    umma_commit_elect(&sm.s_full[1]);
+                    umma_commit_elect(&sm.k_empty[nx]);
+                }
+                PP_TRACE(kt, 5);
+            }
+            umma_commit_elect(&sm.q_free);
+        }
+    } else if (warp < PP_SOFT_WARPS) {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+        // ============================== softmax warps ==============================
+        const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+        const int x = warp >> 3;                      // sub-tile A / B
+        const int lh = (warp >> 2) & 1;               // which 16 lanes of the quarter
+        const int half = lane >> 4;                   // which half of the columns this thread takes
+        const int row = quarter * 32 + lh * 16 + (lane & 15);          // query row inside the sub-tile
+        const uint32_t lane_addr = (uint32_t)(quarter * 32 + lh * 16) << 16;
+        const uint32_t s_x = tmem + lane_addr + PT_S + 64u * x;
+        const uint32_t o_x = tmem + lane_addr + PT_O + 128u * x;
+        const uint32_t q_x = tmem + lane_addr + PT_Q + 64u * x;
+        const int kp0 = half * NP;                    // first key pair of this thread inside a tile
+        const int dbg = p.dbg;
+        const bool pv3 = p.pv_terms > 2;
+        const int N = p.N;
+        long long pos = lo;
+        PpSeg s;
+        uint32_t kt = 0;
+        for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
+            const int b = s.blk / p.NRB, rb = s.blk - b * p.NRB;
+            const size_t q128 = (size_t)b * (2 * p.NRB) + 2 * rb + x;
+            const size_t kt0 = (size_t)b * (4 * p.NRB);
+            const int grow = (2 * rb + x) * PP_SUB + row;
+            const int qrow = min(grow, N - 1);
+            // ---- Q_hi rows -> TMEM (this thread: 32 of the 64 words of its row) ----
+            {
+                const uint4* qsrc = reinterpret_cast<const uint4*>(p.Qw + q128 * PP_QTILE_BYTES + (size_t)row * 256 + half * 128);
+                uint32_t r[32];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const uint4 v4 = __ldg(qsrc + i);
+                    r[4 * i] = v4.x; r[4 * i + 1] = v4.y; r[4 * i + 2] = v4.z; r[4 * i + 3] = v4.w;
+                }
+                tmem_st_h32<32>(q_x, r);
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.q_full[x]);
+            }
+            float2 qp[6];
+            {
+                const int qpr = (qrow & 63) >> 1;
+                const float* pp = p.Pw + (kt0 + (qrow >> 6)) * PP_PTS_FLOATS + qpr * 12 + (qpr >= 16 ? 4 : 0) + (qrow & 1);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) qp[i] = make_float2(pp[2 * i], pp[2 * i]);
+            }
+            float m = 0.f, l = 0.f;                   // reference max (log2 units; compat = 0 keys sit at 0) and row sum
+            const int n = s.j1 - s.j0;
+            for (int t = 0; t < n; ++t, ++kt) {
+                const int st = kt & 1;
+                const int j = s.j0 + t;
+                // compatibilities of this thread's row against its 32 keys (needs only the points)
+                float2 e[NP];
+                mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1);
+                if (dbg & 1) {
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) e[i] = make_float2(0.5f, 0.25f);
+                } else {
+                    pp_compat_pairs<NP>(&sm.pts[st][kp0 * 3 + half], qp, e);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.pts_empty[st]);
+                if ((warp & 7) == 0) PP_TRACE(kt, 6 + x);
+                mbar_wait_role(&sm.s_full[x], kt & 1);
+                if ((warp & 7) == 0) PP_TRACE(kt, 8 + x);
+                tc_fence_after();
+                // e = compat * S - m  (log2 units), and its maximum over this row's keys
+                float emax = -INFINITY;
+                {
+                    uint32_t r[32];
+                    tmem_ld_h32<32>(s_x, r);
+                    tmem_ld_wait();
+                    const float2 neg_m = make_float2(-m, -m);
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) {
+                        const float2 ev = __ffma2_rn(e[i], make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), neg_m);
+                        e[i] = ev;
+                        emax = fmaxf(emax, fmaxf(ev.x, ev.y));
+                    }
+                }
+                const int nvalid = N - j * PP_BN;      // keys of this tile that exist
+                if (nvalid < PP_BN) {                  // last, partial tile: keys past N do not exist
+                    emax = -INFINITY;
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) {
+                        const int key = half * 32 + 2 * i;
+                        if (key >= nvalid) e[i].x = -INFINITY;
+                        if (key + 1 >= nvalid) e[i].y = -INFINITY;
+                        emax = fmaxf(emax, fmaxf(e[i].x, e[i].y));
+                    }
+                }
+                emax = fmaxf(emax, __shfl_xor_sync(0xffffffffu, emax, 16));   // the other half of the row
+                // Lazy reference max: raised only when the row maximum exceeds it by more than 2^8; on
+                // the first tile it is also lowered for rows whose logits are all far below zero.
+                const bool need = (emax > PP_RESCALE_LOG2) || (t == 0 && emax < -PP_RESCALE_LOG2 && emax > -INFINITY);
+                if (__any_sync(0xffffffffu, need)) {
+                    const float shift = need ? emax : 0.f;
+                    const float f = fast_exp2(-shift);
+                    m += shift;
+                    l *= f;
+                    const float2 ns = make_float2(-shift, -shift);
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) e[i] = __fadd2_rn(e[i], ns);
+                    if (t > 0) {
+                        mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);      // PV(t-1) has finished accumulating into O
+                        tc_fence_after();
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) {
+                            uint32_t r[32];
+                            tmem_ld_h32<64>(o_x + 32u * c, r);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
+                            tmem_st_h32<64>(o_x + 32u * c, r);
+                        }
+                    }
+                }
+                // P = exp2(e) as fp16 pairs, two keys per TMEM column: hi at S columns [0,32), and (when the
+                // P_lo V_hi term is issued) the fp16 remainder lo at [32,64).  Without P_lo the row sum is
+                // taken over the ROUNDED weights, so numerator and denominator use the same weights.
+                float2 psum = make_float2(0.f, 0.f);
+                if (pv3) {
+                    uint32_t phi[NP], plo[NP];
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) {
+                        const float2 ev = e[i];
+                        const float2 pr = (dbg & 2) ? make_float2(1.0f + 1e-3f * ev.x, 1.0f + 1e-3f * ev.y)
+                                                    : make_float2(fast_exp2(ev.x), fast_exp2(ev.y));
+                        psum = __fadd2_rn(psum, pr);
+                        phi[i] = pack_half2(pr.x, pr.y);
+                        const float2 back = unpack_half2(phi[i]);
+                        const float2 rem = __fadd2_rn(pr, make_float2(-back.x, -back.y));
+                        plo[i] = pack_half2(rem.x, rem.y);
+                    }
+                    tmem_st_h16<16>(s_x, phi);
+                    tmem_st_h16<16>(s_x + 32u, plo);
+                } else {
+                    uint32_t phi[NP];
+#pragma unroll
+                    for (int i = 0; i < NP; ++i) {
+                        const float2 ev = e[i];
+                        const float2 pr = (dbg & 2) ? make_float2(1.0f + 1e-3f * ev.x, 1.0f + 1e-3f * ev.y)
+                                                    : make_float2(fast_exp2(ev.x), fast_exp2(ev.y));
+                        phi[i] = pack_half2(pr.x, pr.y);
+                        psum = __fadd2_rn(psum, unpack_half2(phi[i]));
+                    }
+                    tmem_st_h16<16>(s_x, phi);
+                }
+                l += psum.x + psum.y;
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.p_full[x]);
+                if ((warp & 7) == 0) PP_TRACE(kt, 10 + x);
+            }
+            // ---- epilogue of the segment ----
+            l += __shfl_xor_sync(0xffffffffu, l, 16);
+            mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);
+            tc_fence_after();
+            if (s.j0 == 0 && s.j1 == NT) {
+                // all keys seen: msg = O / l, this thread writes 64 channels of its row
+                const float inv_l = 1.0f / l;
+                float* orow = p.out + ((size_t)b * N + qrow) * p.ld_out + half * 64;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_h32<64>(o_x + 32u * c, r);
+                    tmem_ld_wait();
+                    if (grow < N) {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            float4 o;
+                            o.x = __uint_as_float(r[i]) * inv_l;
+                            o.y = __uint_as_float(r[i + 1]) * inv_l;
+                            o.z = __uint_as_float(r[i + 2]) * inv_l;
+                            o.w = __uint_as_float(r[i + 3]) * inv_l;
+                            *reinterpret_cast<float4*>(orow + c * 32 + i) = o;
+                        }
+                    }
+                }
+            } else {
+                // partial: store (O, m, l); the last contributor of the block combines all partials
+                const size_t base = ((size_t)(cta * 2 + (si == 0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                float* po = p.part_o + base * PP_C + half * 64;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_h32<64>(o_x + 32u * c, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4)
+                        *reinterpret_cast<uint4*>(po + c * 32 + i) = make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+                }
+                if (half == 0) {
+                    p.part_ml[base * 2] = m;
+                    p.part_ml[base * 2 + 1] = l;
+                }
+                __threadfence();
+                named_bar_sync(1 + x, 256);
+                if ((warp & 7) == 0 && lane == 0) last_flag[x] = atomicAdd(&p.counters[s.blk * 2 + x], 1);
+                named_bar_sync(1 + x, 256);
+                const long long T = p.total_steps, x0 = (long long)s.blk * NT;
+                const int c_first = (int)(((x0 + 1) * G + T - 1) / T) - 1;
+                const int c_last = (int)(((x0 + NT) * G + T - 1) / T) - 1;
+                if (last_flag[x] == c_last - c_first) {
+                    __threadfence();
+                    float M = -INFINITY;
+                    for (int c = c_first; c <= c_last; ++c) {
+                        const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                        M = fmaxf(M, pp_ldcg(p.part_ml + idx * 2));
+                    }
+                    float L = 0.f;
+                    for (int c = c_first; c <= c_last; ++c) {
+                        const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                        L += exp2f(pp_ldcg(p.part_ml + idx * 2) - M) * pp_ldcg(p.part_ml + idx * 2 + 1);
+                    }
+                    const float inv_l = 1.0f / L;
+                    float* orow = p.out + ((size_t)b * N + qrow) * p.ld_out + half * 64;
+#pragma unroll 1
+                    for (int ch = 0; ch < 64; ch += 16) {
+                        float acc[16];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+                        for (int c = c_first; c <= c_last; ++c) {
+                            const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                            const float f = exp2f(pp_ldcg(p.part_ml + idx * 2) - M);
+                            const float* src_o = p.part_o + idx * PP_C + half * 64 + ch;
+#pragma unroll
+                            for (int i = 0; i < 16; i += 4) {
+                                const float4 v4 = pp_ldcg4(src_o + i);
+                                acc[i] += f * v4.x; acc[i + 1] += f * v4.y; acc[i + 2] += f * v4.z; acc[i + 3] += f * v4.w;
+                            }
+                        }
+                        if (grow < N) {
+#pragma unroll
+                            for (int i = 0; i < 16; i += 4)
+                                *reinterpret_cast<float4*>(orow + ch + i) = make_float4(acc[i] * inv_l, acc[i + 1] * inv_l, acc[i + 2] * inv_l, acc[i + 3] * inv_l);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == PP_SOFT_WARPS + 1) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+static int pp_grid(int B, int NRB, int NT) {
+    const long long total = (long long)B * NRB * NT;
+    // PDSC_ATTN_GRID (read per call; a test/tuning knob): unset = one CTA per SM (stream-K),
+    // 0 = one CTA per 256-row block (no partials), n = n CTAs
+    const char* e = getenv("PDSC_ATTN_GRID");
+    const int knob = e ? atoi(e) : -1;
+    long long g = knob < 0 ? num_sms() : (knob == 0 ? (long long)B * NRB : knob);
+    if (g > total) g = total;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+struct PpLayout {
+    size_t q, k, v, pts, part_o, part_ml, counters, total;
+};
+static PpLayout pp_layout(int B, int N) {
+    const int NRB = (N + PP_BM - 1) / PP_BM, NT = (N + PP_BN - 1) / PP_BN;
+    const size_t t128 = (size_t)B * 2 * NRB;
+    const size_t G = (size_t)pp_grid(B, NRB, NT);
+    PpLayout L;
+    size_t off = 0;
+    L.q = off; off += t128 * PP_QTILE_BYTES;
+    L.k = off; off += t128 * 2 * PP_KTILE_BYTES;
+    L.v = off; off += t128 * 2 * PP_VTILE_BYTES;
+    L.pts = off; off += align_up(t128 * 2 * PP_PTS_BYTES, 1024);
+    L.part_o = off; off += G * 2 * 2 * PP_SUB * PP_C * sizeof(float);
+    L.part_ml = off; off += G * 2 * 2 * PP_SUB * 2 * sizeof(float);
+    L.counters = off; off += align_up((size_t)B * NRB * 2 * sizeof(int), 1024);
+    L.total = off + 1024;
+    return L;
+}
+
+size_t attn_pp_workspace(int B, int N) { return pp_layout(B, N).total; }
+
+int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
+                   float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
+                   size_t ws_bytes, cudaStream_t st) {
+    if (C != PP_C) { set_error("nonlocal_attn: C=%d unsupported (kernels are built for C=%d)", C, PP_C); return PDSC_ERR_ARG; }
+    const PpLayout L = pp_layout(B, N);
+    if (!ws || ws_bytes < L.total) {
+        set_error("nonlocal_attn: workspace too small (%zu < %zu)", ws_bytes, L.total);
+        return PDSC_ERR_WORKSPACE;
+    }
+    const int NRB = (N + PP_BM - 1) / PP_BM, NT = (N + PP_BN - 1) / PP_BN;
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+    PpParams p;
+    p.Qw = base + L.q; p.Kw = base + L.k; p.Vw = base + L.v;
+    p.Pw = reinterpret_cast<const float*>(base + L.pts);
+    p.out = out; p.ld_out = ld_out;
+    p.part_o = reinterpret_cast<float*>(base + L.part_o);
+    p.part_ml = reinterpret_cast<float*>(base + L.part_ml);
+    p.counters = reinterpret_cast<int*>(base + L.counters);
+    p.N = N; p.NRB = NRB; p.NT = NT;
+    p.total_steps = (long long)B * NRB * NT;
+    // PDSC_ATTN_SPLIT16: all three hi/lo terms for both contractions.  PDSC_ATTN_PV_TERMS=2 (tuning knob) drops
+    // the P_lo V_hi term and takes the row sum over the rounded P_hi: ~2e-4 relative message error.
+    // PDSC_ATTN_FP16: hi*hi only.
+    p.qk_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
+    p.pv_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
+    if (mode == PDSC_ATTN_SPLIT16) { const char* e = getenv("PDSC_ATTN_PV_TERMS"); if (e && atoi(e) >= 1 && atoi(e) <= 3) p.pv_terms = atoi(e); }
+    static int dbg = -1;                            // PDSC_ATTN_DBG: timing experiments only (results are wrong)
+    if (dbg < 0) { const char* e = getenv("PDSC_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
+    p.dbg = dbg;
+    if (dbg & 4) p.qk_terms = p.pv_terms = 0;       // no MMAs
+    const int smem_bytes = (int)sizeof(PpSmem) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(attn_pp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
+        cudaFuncSetAttribute(attn_pp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        attr_set = true;
+    }
+    const int G = pp_grid(B, NRB, NT);
+    cudaMemsetAsync(p.counters, 0, (size_t)B * NRB * 2 * sizeof(int), st);
+    const float qscale = 1.4426950408889634f / sqrtf((float)C);
+    attn_pp_prep_kernel<<<dim3(2 * NRB, B), 256, 128 * 129 * 4, st>>>(
+        q, k, v, ld, src, tgt, N, 2 * NRB, qscale, 1.0f / sigma_spat, const_cast<uint8_t*>(p.Qw), const_cast<uint8_t*>(p.Kw),
+        const_cast<uint8_t*>(p.Vw), const_cast<float*>(p.Pw));
+    p.trace = nullptr;
+    const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
+    if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
+    attn_pp_kernel<<<G, PP_THREADS, smem_bytes, st>>>(p);
+    if (trace_path) {
+        static long long h[16 * 256];
+        cudaDeviceSynchronize();
+        cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(trace_path, "w")) {
+            fprintf(f, "# step kIssued vIssued pfullA pfullB issuedA issuedB compatA compatB sSeenA sSeenB pArrA pArrB vfull kfullNext (clocks relative to step 0 kIssued)\n");
+            for (int i = 0; i < 256 && h[i * 16]; ++i) {
+                fprintf(f, "%d", i);
+                for (int e = 0; e < 14; ++e) fprintf(f, " %lld", h[i * 16 + e] ? h[i * 16 + e] - h[0] : -1);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+        cudaFree(p.trace);
+    }
+    count_launches(2);
+    return check_launch("nonlocal_attn(tcgen05 ping-pong)");
+}
+
+}  // namespace pdsc

@@ -59,6 +59,20 @@ __device__ __forceinline__ void mbar_wait_role(uint64_t* bar, uint32_t parity) {
         if (spin > (1u << 22)) __trap();
     }
 }
+// Whole spin loop inside one asm statement: the compiler sees no data-dependent branch, so a warp that
+// waits with all its lanes stays provably convergent (values derived from uniform inputs can then live
+// in uniform registers, which is what tcgen05.mma operands want).
+__device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra WAIT_DONE_%=;\n\t"
+        "bra WAIT_LOOP_%=;\n\t"
+        "WAIT_DONE_%=:\n\t}"
+        ::"r"(smem_u32(bar)), "r"(parity), "r"(20000u)
+        : "memory");
+}
 
 // ---- bulk async copy global -> shared (TMA engine, no tensor map) ----------------------------------
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
@@ -116,6 +130,32 @@ __device__ __forceinline__ void umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
         "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
+}
+// Whole-warp forms: every lane executes the statement (control flow stays warp-uniform, operands can live in
+// uniform registers), one elected lane issues the instruction.
+__device__ __forceinline__ void umma_ss_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, pe;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_ts_elect(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, pe;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
 }
 // Arrives on the mbarrier when all previously issued tcgen05 async ops of this thread complete.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {

@@ -270,9 +270,16 @@ def _attn_ref(qkv, src, tgt, sigma):
     return torch.cat(outs)
 
 
-@pytest.mark.parametrize("N", [128, 1, 100, 129, 256, 700])
-def test_attention_split16_vs_oracle(N):
+@pytest.mark.parametrize("grid", [None, "0", "5", "7"])
+@pytest.mark.parametrize("N", [128, 1, 100, 129, 256, 257, 700, 1100])
+def test_attention_split16_vs_oracle(N, grid, monkeypatch):
+    """grid: None = stream-K over all SMs (partials + last-arriver combine), "0" = one CTA per 256-row
+    block (no partials), "5"/"7" = a few CTAs whose ranges cut blocks at odd places."""
     from pointdsc_b200 import _cabi
+    if grid is None:
+        monkeypatch.delenv("PDSC_ATTN_GRID", raising=False)
+    else:
+        monkeypatch.setenv("PDSC_ATTN_GRID", grid)
     g = torch.Generator().manual_seed(1000 + N)
     C, B = 128, 2
     qkv = torch.randn(B, N, 3 * C, generator=g)
@@ -283,7 +290,7 @@ def test_attention_split16_vs_oracle(N):
     torch.cuda.synchronize()
     ref = _attn_ref(qkv, src, tgt, 0.1)
     err = (out.cpu() - ref).abs().max().item()
-    print(f"split16 attention N={N}: max abs err {err:.3e}")
+    print(f"split16 attention N={N} grid={grid}: max abs err {err:.3e}")
     assert err < 5e-5
 
 
