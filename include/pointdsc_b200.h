@@ -78,6 +78,20 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
 int pdsc_split16_rows(const float* x, const float* add, float* y_out, void* out16, int64_t rows, int K, int Kp,
                       int relu, void* stream);
 
+/* Fused pointwise MLP chain for the channel-last 1x1-conv stacks (PointCN models/PointDSC.py:54-62,
+ *  NonLocalBlock.fc_message + residual :12-18,44): y = L_{n-1}(..L_0(x + add_in)..) + add_out with
+ *  L_i(v) = act_i(v W_i + b_i), computed on the tensor cores with fp16 hi/lo split operands and fp32 accumulation
+ *  (fp32-grade accuracy), one 128-row tile kept on chip through the whole chain.
+ *  x, add_in (nullable): fp32 [rows, dims[0]]; add_out (nullable), y_out (nullable): fp32 [rows, dims[n_layers]];
+ *  y_packed (nullable): fp16 [rows, Kp] in the pdsc_split16_rows row layout (operand of a following library GEMM).
+ *  dims (n_layers + 1 entries, each 64 or 128) and relu (n_layers flags) are HOST arrays; n_layers <= 3.
+ *  wpack (device): per layer the tcgen05 B-operand image of W_i (BatchNorm folded): fp16 hi then fp16 lo, each
+ *  dims[i]/64 blocks of [dims[i+1] rows x 64 input channels], 128-byte rows with the 128B swizzle (16-byte chunk c of
+ *  row r stored at chunk c ^ (r & 7)).  bias (device): the b_i concatenated, fp32. */
+int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_layers, const int32_t* dims,
+                   const int32_t* relu, const void* wpack, const float* bias, const float* add_out,
+                   float* y_out, void* y_packed, int Kp, void* stream);
+
 /* (c) NMS seed picking; replaces PointDSC.pick_seeds models/PointDSC.py:199-217.
  *  is_local_max[i] = all_j (score_i >= score_j  or  |s_i-s_j| >= R);
  *  seeds = first S indices ordered by (score*is_local_max descending, index ascending).

@@ -40,6 +40,8 @@ SIGNATURES = {
     "pdsc_post_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
                                  c_void_p]),
     "pdsc_split16_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    "pdsc_mlp_chain": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p, c_int, c_void_p]),
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                    c_void_p, c_void_p]),
     "pdsc_power_normalize": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -169,6 +171,54 @@ def split16_rows(x, add=None, relu=False, y_out=None, out16=None):
     _check(rc, "pdsc_split16_rows")
     _count()
     return out16
+
+
+class MlpChain:
+    """Device-side description of a fused pointwise MLP chain (pdsc_mlp_chain): pre-packed weights + biases."""
+
+    def __init__(self, layers, relu):
+        """layers: list of (Wt [K,N] fp32 with BatchNorm folded, b [N] fp32) on the target device; relu: flags."""
+        self.dims = [int(layers[0][0].shape[0])] + [int(Wt.shape[1]) for Wt, _ in layers]
+        self.relu = [1 if r else 0 for r in relu]
+        self.c_dims = (ctypes.c_int32 * len(self.dims))(*self.dims)
+        self.c_relu = (ctypes.c_int32 * len(self.relu))(*self.relu)
+        self.wpack = torch.cat([pack_umma_b(Wt) for Wt, _ in layers]).contiguous()
+        self.bias = torch.cat([b.float() for _, b in layers]).contiguous()
+
+
+def pack_umma_b(Wt):
+    """[K,N] fp32 (y = x @ Wt) -> uint8 image of the tcgen05 B operand: fp16 hi then fp16 lo, each K/64 blocks of
+    [N rows x 64 input channels] with 128-byte rows and the 128B swizzle (16-byte chunk c of row r at c ^ (r & 7))."""
+    K, N = Wt.shape
+    W = Wt.t().contiguous().float()                 # [N, K]: row n = output channel, K contiguous (K-major)
+    hi = W.half()
+    lo = (W - hi.float()).half()
+    r7 = (torch.arange(N, device=W.device) & 7)[:, None]
+    pos = torch.arange(8, device=W.device)[None, :] ^ r7           # chunk stored at position p holds source chunk p ^ (r & 7)
+    idx = pos[:, None, :, None].expand(N, K // 64, 8, 8)
+    out = []
+    for h in (hi, lo):
+        blocks = h.reshape(N, K // 64, 8, 8).gather(2, idx)        # [n, kc, position, element]
+        out.append(blocks.permute(1, 0, 2, 3).contiguous().view(torch.uint8).reshape(-1))
+    return torch.cat(out)
+
+
+def mlp_chain(x, chain, add_in=None, add_out=None, want_y=True, want_packed=False):
+    """y = chain(x + add_in) + add_out; returns (y fp32 or None, packed fp16 [rows, split_kp(N)] or None)."""
+    lib = load()
+    rows, K = x.shape
+    assert K == chain.dims[0]
+    N = chain.dims[-1]
+    y = torch.empty(rows, N, dtype=torch.float32, device=x.device) if want_y else None
+    Kp = split_kp(N)
+    yp = torch.empty(rows, Kp, dtype=torch.float16, device=x.device) if want_packed else None
+    rc = lib.pdsc_mlp_chain(_ptr(x, torch.float32, "x"), _ptr(add_in, torch.float32, "add_in"), rows, len(chain.relu),
+                            ctypes.cast(chain.c_dims, c_void_p), ctypes.cast(chain.c_relu, c_void_p),
+                            _ptr(chain.wpack, torch.uint8, "wpack"), _ptr(chain.bias, torch.float32, "bias"),
+                            _ptr(add_out, torch.float32, "add_out"), _ptr(y), _ptr(yp), Kp, _stream())
+    _check(rc, "pdsc_mlp_chain")
+    _count()
+    return y, yp
 
 
 def pick_seeds(src, scores, R, S, ws=None, want_aux=False):

@@ -107,6 +107,18 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
     return PDSC_ERR_ARG;
 }
 
+int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_layers, const int32_t* dims,
+                   const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y_out,
+                   void* y_packed, int Kp, void* stream) {
+    PDSC_REQUIRE(x && dims && relu && wpack && bias && (y_out || y_packed), "mlp_chain: null pointer");
+    PDSC_REQUIRE(rows > 0, "mlp_chain: rows must be positive");
+    PDSC_REQUIRE(aligned16(x) && aligned16(wpack) && (!add_in || aligned16(add_in)) && (!add_out || aligned16(add_out)) &&
+                     (!y_out || aligned16(y_out)) && (!y_packed || aligned16(y_packed)),
+                 "mlp_chain: pointers must be 16-byte aligned");
+    return launch_mlp_chain(x, add_in, rows, n_layers, dims, relu, wpack, bias, add_out, y_out, y_packed, Kp,
+                            reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds_out,
                     uint8_t* is_local_max_out, int32_t* n_pos_out, void* ws, size_t ws_bytes, void* stream) {
     PDSC_REQUIRE(src && scores && seeds_out && ws, "pick_seeds: null pointer");

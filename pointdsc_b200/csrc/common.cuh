@@ -208,6 +208,9 @@ int launch_compat_matvec(const float* src, const float* tgt, const float* v, flo
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st);
 int launch_split16_rows(const float* x, const float* add, float* y_out, void* out16, long long rows, int K, int Kp,
                         int relu, cudaStream_t st);
+int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_layers, const int32_t* dims,
+                     const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y,
+                     void* y_packed, int Kp, cudaStream_t st);
 size_t power_workspace(int N);
 int power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
                     int32_t* iters_out, void* ws, size_t ws_bytes, cudaStream_t st);

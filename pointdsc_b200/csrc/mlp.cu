@@ -1,0 +1,225 @@
+// Fused channel-last pointwise MLP chains on the tensor cores (tcgen05, fp16 hi/lo split, fp32 accumulate).
+// The 1x1-conv stacks of the reference -- PointCN (Conv1d+BN+ReLU, models/PointDSC.py:54-62) and
+// NonLocalBlock.fc_message (Conv+BN+ReLU, Conv+BN+ReLU, Conv, :12-18) with the residual add (:44) -- are
+// chains of tiny GEMMs (K, N <= 128) over B*N rows: as separate library GEMMs every activation makes an HBM
+// round trip (plus one more for the operand packing).  Here one CTA keeps a 128-row tile on chip through the
+// whole chain:
+//     x (+add_in) -> [ W_0, b_0, ReLU? ] -> ... -> [ W_{L-1}, b_{L-1}, ReLU? ] (+add_out) -> y
+//   thread t <-> row t: loads its fp32 row, splits it into fp16 hi + lo and stores both to TMEM as the A operand;
+//   an elected lane issues hi*hi + hi*lo + lo*hi tcgen05.mma against the pre-packed weights in shared memory
+//   (K-major, 128B swizzle, BatchNorm folded); the fp32 accumulator comes back through tcgen05.ld for bias / ReLU
+//   and is split again as the next layer's A operand.  Nothing but x and y touches HBM.
+// Accuracy is that of the three-term split (22 mantissa bits per operand), same as pdsc_split16_rows + fp16 GEMM.
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace pdsc {
+
+using namespace sm100;
+
+constexpr int ML_MAX_LAYERS = 3;
+constexpr int ML_THREADS = 128;
+constexpr uint32_t ML_A_LO = 64;      // TMEM columns: A hi [0,64), A lo [64,128), D [128,256)
+constexpr uint32_t ML_D = 128;
+
+struct MlpParams {
+    const float* x; const float* add_in; const float* add_out;
+    float* y; uint8_t* y_packed;
+    const uint8_t* wpack; const float* bias;
+    long long rows;
+    int n_layers;
+    int K[ML_MAX_LAYERS], N[ML_MAX_LAYERS], relu[ML_MAX_LAYERS];
+    uint32_t w_off[ML_MAX_LAYERS];     // byte offset of the layer's hi image inside wpack; lo image follows it
+    uint32_t b_off[ML_MAX_LAYERS];     // float offset of the layer's bias
+    uint32_t w_bytes, n_bias;
+    int Kp;                            // row length (halves) of the packed output
+};
+
+__device__ __forceinline__ uint64_t ml_uniform64(uint64_t v) {   // broadcast from lane 0: provably warp-uniform
+    const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)v, 0), hi = __shfl_sync(0xffffffffu, (uint32_t)(v >> 32), 0);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ void ml_split_pair(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = pack_half2(a, b);
+    const float2 back = unpack_half2(hi);
+    lo = pack_half2(a - back.x, b - back.y);
+}
+
+__global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* bsm = reinterpret_cast<float*>(wsm + p.w_bytes);
+    __shared__ uint64_t w_bar, mma_bar;
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&w_bar, 1);
+        mbar_init(&mma_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    // weights: one bulk copy per CTA (they stay resident while the CTA walks its row tiles)
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&w_bar, p.w_bytes);
+        for (uint32_t off = 0; off < p.w_bytes; off += 32768u) {
+            const uint32_t n = min(32768u, p.w_bytes - off);
+            bulk_g2s(wsm + off, p.wpack + off, n, &w_bar);
+        }
+    }
+    for (uint32_t i = threadIdx.x; i < p.n_bias; i += ML_THREADS) bsm[i] = p.bias[i];
+    __syncthreads();
+    mbar_wait_role(&w_bar, 0);
+
+    uint32_t mma_phase = 0;
+    const long long n_tiles = (p.rows + 127) / 128;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long row = tile * 128 + threadIdx.x;
+        const bool live = row < p.rows;
+        const long long rrow = live ? row : p.rows - 1;
+        // ---- input row -> A operand (hi, lo) in TMEM ----
+        {
+            const int K0 = p.K[0];
+            const float4* xr = reinterpret_cast<const float4*>(p.x + rrow * K0);
+            const float4* ar = p.add_in ? reinterpret_cast<const float4*>(p.add_in + rrow * K0) : nullptr;
+            for (int c = 0; c < K0 / 32; ++c) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float4 v = __ldg(xr + c * 8 + i);
+                    if (ar) { const float4 a = __ldg(ar + c * 8 + i); v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w; }
+                    ml_split_pair(v.x, v.y, hi[2 * i], lo[2 * i]);
+                    ml_split_pair(v.z, v.w, hi[2 * i + 1], lo[2 * i + 1]);
+                }
+                tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
+                tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
+            }
+        }
+        for (int l = 0; l < p.n_layers; ++l) {
+            const int K = p.K[l], N = p.N[l];
+            tmem_st_wait();
+            tc_fence_before();
+            __syncthreads();           // every row's A operand is in TMEM, and everyone is done reading D
+            if (warp == 0) {
+                tc_fence_after();
+                const uint32_t idesc = umma_idesc_f16(128, N);
+                const uint32_t blk = (uint32_t)N * 128u;                  // bytes of one 64-channel B block
+                const uint32_t lo_off = (uint32_t)(K / 64) * blk;         // lo image follows the hi image
+                const uint64_t wd = ml_uniform64(umma_desc_sw128_kmajor(smem_u32(wsm + p.w_off[l])));
+                uint32_t acc = 0;
+                for (int term = 0; term < 3; ++term) {
+                    const uint32_t a0 = tmem + (term == 2 ? ML_A_LO : 0u);
+                    const uint32_t b0 = term == 1 ? lo_off : 0u;
+                    for (int kk = 0; kk < K / 16; ++kk) {
+                        const uint64_t db = wd + (uint64_t)((b0 + (uint32_t)(kk >> 2) * blk + (uint32_t)(kk & 3) * 32u) >> 4);
+                        umma_ts_elect(tmem + ML_D, a0 + (uint32_t)kk * 8u, db, idesc, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit_elect(&mma_bar);
+            }
+            mbar_wait_role(&mma_bar, mma_phase);
+            mma_phase ^= 1;
+            tc_fence_after();
+            const bool last = l + 1 == p.n_layers;
+            const float* bias = bsm + p.b_off[l];
+            for (int c = 0; c < N / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld32(tmem + lane_addr + ML_D + (uint32_t)c * 32u, r);
+                tmem_ld_wait();
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    v[i] = __uint_as_float(r[i]) + bias[c * 32 + i];
+                    if (p.relu[l]) v[i] = fmaxf(v[i], 0.f);
+                }
+                if (!last) {
+                    uint32_t hi[16], lo[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+                    tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
+                    tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
+                } else {
+                    if (p.add_out) {
+                        const float4* ar = reinterpret_cast<const float4*>(p.add_out + rrow * N + c * 32);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float4 a = __ldg(ar + i);
+                            v[4 * i] += a.x; v[4 * i + 1] += a.y; v[4 * i + 2] += a.z; v[4 * i + 3] += a.w;
+                        }
+                    }
+                    if (live && p.y) {
+                        float4* yr = reinterpret_cast<float4*>(p.y + row * N + c * 32);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) yr[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                    }
+                    if (live && p.y_packed) {
+                        // row layout of pdsc_split16_rows: [hi(N) | hi(N) | lo(N) | 1 1 0 ..]
+                        uint8_t* pr = p.y_packed + (size_t)row * p.Kp * 2;
+                        uint32_t hi[16], lo[16];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const uint4 h4 = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
+                            const uint4 l4 = make_uint4(lo[4 * i], lo[4 * i + 1], lo[4 * i + 2], lo[4 * i + 3]);
+                            *reinterpret_cast<uint4*>(pr + (c * 32 + i * 8) * 2) = h4;
+                            *reinterpret_cast<uint4*>(pr + (N + c * 32 + i * 8) * 2) = h4;
+                            *reinterpret_cast<uint4*>(pr + (2 * N + c * 32 + i * 8) * 2) = l4;
+                        }
+                        if (c == 0) {
+                            // tail: 1 1 0 0 0 ... (Kp - 3N halves, a multiple of 8)
+                            for (int h8 = 0; h8 < (p.Kp - 3 * N) / 8; ++h8)
+                                *reinterpret_cast<uint4*>(pr + (3 * N + h8 * 8) * 2) = make_uint4(h8 == 0 ? 0x3c003c00u : 0u, 0u, 0u, 0u);
+                        }
+                    }
+                }
+            }
+        }
+        // the next tile's A stores must not overtake this tile's last MMA: it has completed (mma_bar), and D reads
+        // are ordered by the __syncthreads at the top of the next layer loop
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_layers, const int32_t* dims,
+                     const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y,
+                     void* y_packed, int Kp, cudaStream_t st) {
+    if (n_layers < 1 || n_layers > ML_MAX_LAYERS) { set_error("mlp_chain: 1..%d layers supported", ML_MAX_LAYERS); return PDSC_ERR_ARG; }
+    MlpParams p;
+    p.x = x; p.add_in = add_in; p.add_out = add_out; p.y = y; p.y_packed = reinterpret_cast<uint8_t*>(y_packed);
+    p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.rows = rows; p.n_layers = n_layers; p.Kp = Kp;
+    uint32_t woff = 0, boff = 0;
+    for (int l = 0; l < n_layers; ++l) {
+        const int K = dims[l], N = dims[l + 1];
+        if ((K != 64 && K != 128) || (N != 64 && N != 128)) { set_error("mlp_chain: layer dims must be 64 or 128 (got %d -> %d)", K, N); return PDSC_ERR_ARG; }
+        p.K[l] = K; p.N[l] = N; p.relu[l] = relu[l];
+        p.w_off[l] = woff; p.b_off[l] = boff;
+        woff += 2u * (uint32_t)(K / 64) * (uint32_t)N * 128u;     // hi + lo images
+        boff += (uint32_t)N;
+    }
+    p.w_bytes = woff; p.n_bias = boff;
+    if (y_packed && (Kp % 8 != 0 || Kp < 3 * dims[n_layers] + 8)) { set_error("mlp_chain: bad packed row length %d", Kp); return PDSC_ERR_ARG; }
+    const int smem = (int)(p.w_bytes + p.n_bias * sizeof(float) + 1024);
+    static int smem_set = 0;
+    if (smem > smem_set) {
+        cudaFuncSetAttribute(mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        smem_set = smem;
+    }
+    const long long n_tiles = (rows + 127) / 128;
+    const int per_sm = smem <= 100 * 1024 ? 2 : 1;                 // TMEM: 256 of 512 columns per CTA
+    long long grid = (long long)num_sms() * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    mlp_chain_kernel<<<(int)grid, ML_THREADS, smem, st>>>(p);
+    count_launches(1);
+    return check_launch("mlp_chain");
+}
+
+}  // namespace pdsc

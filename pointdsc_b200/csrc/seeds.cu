@@ -16,7 +16,7 @@ constexpr int NMS_THREADS = 256;
 constexpr int NMS_TILE = 1024;
 
 __global__ void __launch_bounds__(NMS_THREADS) nms_kernel(const float* __restrict__ src,
-                                                          const float* __restrict__ scores, int N, float R,
+                                                          const float* __restrict__ scores, int N, float T2,
                                                           int jchunk, int32_t* __restrict__ suppressed) {
     __shared__ float4 tile[NMS_TILE];
     const int b = blockIdx.z;
@@ -39,9 +39,11 @@ __global__ void __launch_bounds__(NMS_THREADS) nms_kernel(const float* __restric
 #pragma unroll 4
         for (int t = 0; t < nj; ++t) {
             const float4 p = tile[t];
-            const bool ge_score = si >= p.w;
-            const bool far = dist3(xi, yi, zi, p.x, p.y, p.z) >= R;
-            sup |= !(ge_score || far);
+            // sqrt(d2) >= R  <=>  d2 >= T2 (T2 = smallest fp32 whose correctly rounded sqrt reaches R, found on
+            // the host), with d2 rounded exactly like torch.norm's mul/add sequence: no sqrt in the loop
+            const float dx = xi - p.x, dy = yi - p.y, dz = zi - p.z;
+            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            sup |= (!(si >= p.w)) & (!(d2 >= T2));   // negated forms keep the reference's NaN behaviour
         }
     }
     if (sup && i < N) suppressed[(size_t)b * N + i] = 1;
@@ -130,7 +132,15 @@ int launch_pick_seeds(const float* src, const float* scores, int B, int N, float
     int jchunk = (N + jsplit - 1) / jsplit;
     jchunk = (jchunk + NMS_TILE - 1) / NMS_TILE * NMS_TILE;
     jsplit = (N + jchunk - 1) / jchunk;
-    nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, R, jchunk, suppressed);
+    // squared-distance threshold equivalent to the reference's `norm >= R` (sqrtf is monotone and correctly rounded)
+    float T2 = R * R;
+    if (R <= 0.f) {
+        T2 = 0.f;                                     // every distance is >= R
+    } else {
+        while (T2 > 0.f && sqrtf(T2) >= R) T2 = nextafterf(T2, 0.f);
+        while (sqrtf(T2) < R) T2 = nextafterf(T2, INFINITY);
+    }
+    nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, T2, jchunk, suppressed);
     const int p2 = next_pow2(N);
     unsigned long long* gbuf = nullptr;
     size_t smem = sizeof(unsigned long long) * (size_t)p2;

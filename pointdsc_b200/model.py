@@ -114,9 +114,11 @@ class PointDSC(nn.Module):
                 nn.init.constant_(m.bias, 0)
         # kernel selection for the attention contraction (include/pointdsc_b200.h PDSC_ATTN_*)
         self.attn_mode = _MODE_NAMES[os.environ.get("POINTDSC_ATTN_MODE", "split16")]
-        # how the 1x1-conv GEMMs run: "split16" = fp16 hi/lo operands on the tensor cores (torch.mm with
-        # fp32 accumulation/output, fp32-grade accuracy), "fp32" = plain fp32 addmm
-        self.mlp_mode = os.environ.get("POINTDSC_MLP_MODE", "split16")
+        # how the 1x1-conv stacks run: "fused" = PointCN and fc_message(+residual) as on-chip tcgen05 chains
+        # (pdsc_mlp_chain), the q/k/v projection as one library GEMM on packed fp16 hi/lo operands;
+        # "split16" = every layer a library GEMM on packed operands (torch.mm, fp32 accumulation/output);
+        # "fp32" = plain fp32 addmm.  All three are fp32-grade accurate.
+        self.mlp_mode = os.environ.get("POINTDSC_MLP_MODE", "fused")
         self._packed = None
         self._ws = _cabi.Workspace()
 
@@ -159,6 +161,10 @@ class PointDSC(nn.Module):
             if L["pcn"][0].is_cuda:
                 for name in ("pcn", "qkv", "m0", "m3", "m6"):
                     L[name + "_s"] = _pack_split(*L[name])
+                if self.num_channels == 128:
+                    # fused on-chip chains (pdsc_mlp_chain): PointCN conv+BN+ReLU, and fc_message + residual
+                    L["pcn_chain"] = _cabi.MlpChain([L["pcn"]], [True])
+                    L["msg_chain"] = _cabi.MlpChain([L["m0"], L["m3"], L["m6"]], [True, True, False])
             layers.append(L)
         P["layers"] = layers
         P["cls"] = [_fold(self.classification[i], None) for i in (0, 2, 4)]
@@ -190,7 +196,9 @@ class PointDSC(nn.Module):
         C = self.num_channels
         W, b = P["layer0"]
         feat = torch.addmm(b, corr_pos.reshape(B * N, -1), W)
-        if self.mlp_mode == "split16" and feat.is_cuda and C % 16 == 0:
+        if self.mlp_mode == "fused" and feat.is_cuda and C == 128:
+            return self._encode_fused(P, feat, src, tgt, B, N, C)
+        if self.mlp_mode in ("split16", "fused") and feat.is_cuda and C % 16 == 0:
             return self._encode_split16(P, feat, src, tgt, B, N, C)
         for L in P["layers"]:
             feat = torch.relu_(torch.addmm(L["pcn"][1], feat, L["pcn"][0]))
@@ -201,6 +209,18 @@ class PointDSC(nn.Module):
             m = torch.relu_(torch.addmm(L["m3"][1], m, L["m3"][0]))
             feat = torch.addmm(feat, m, L["m6"][0]).add_(L["m6"][1])
         return feat.view(B, N, C)
+
+    def _encode_fused(self, P, feat, src, tgt, B, N, C):
+        """Per layer: one fused kernel for PointCN (writes y1 and its packed fp16 hi/lo rows), one library GEMM for
+        the fused q/k/v projection, the attention kernel, one fused kernel for fc_message + residual."""
+        x = feat
+        for L in P["layers"]:
+            y1, y1p = _cabi.mlp_chain(x, L["pcn_chain"], want_y=True, want_packed=True)     # PointCN conv+BN+ReLU
+            qkv = torch.mm(y1p, L["qkv_s"], out_dtype=torch.float32).view(B, N, 3 * C)
+            msg = _cabi.nonlocal_attn(qkv[:, :, 0:C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:3 * C], src, tgt,
+                                      P["sigma_spat"], mode=self.attn_mode, ws=self._ws)
+            x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)          # feat + fc_message(msg)
+        return x.view(B, N, C)
 
     def _encode_split16(self, P, feat, src, tgt, B, N, C):
         """Same layer sequence with every GEMM on the tensor cores: activations are packed to fp16

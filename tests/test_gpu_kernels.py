@@ -352,3 +352,37 @@ def test_split16_rows_gemm_matches_fp64(K, out):
     err = (y.double() - ref).abs().max().item()
     print(f"split16 GEMM K={K}: max abs err {err:.3e} (fp32 addmm: {((v @ Wt + b).double() - ref).abs().max().item():.3e})")
     assert err < 2e-6 * ref.abs().max().item()
+
+
+# ------------------------------------------------------- fused pointwise MLP chains (tcgen05)
+@pytest.mark.parametrize("dims,relu,rows", [((128, 64, 64, 128), (1, 1, 0), 3001), ((128, 128), (1,), 517),
+                                            ((64, 128), (0,), 128), ((128, 64), (1,), 1)])
+def test_mlp_chain_matches_fp64(dims, relu, rows):
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(sum(dims) + rows)
+    x = torch.randn(rows, dims[0], generator=g) * 2
+    add_in = torch.randn(rows, dims[0], generator=g)
+    add_out = torch.randn(rows, dims[-1], generator=g)
+    layers = [(torch.randn(dims[i], dims[i + 1], generator=g) * 0.15, torch.randn(dims[i + 1], generator=g)) for i in range(len(relu))]
+    chain = _cabi.MlpChain([(cu(W), cu(b)) for W, b in layers], relu)
+    y, yp = _cabi.mlp_chain(cu(x), chain, add_in=cu(add_in), add_out=cu(add_out), want_y=True, want_packed=True)
+    torch.cuda.synchronize()
+    v = (x + add_in).double()
+    for (W, b), r in zip(layers, relu):
+        v = v @ W.double() + b.double()
+        if r:
+            v = torch.relu(v)
+    ref = v + add_out.double()
+    err = (y.cpu().double() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    print(f"mlp_chain {dims}: max abs err {err:.3e} (scale {scale:.2f})")
+    assert err < 2e-6 * max(1.0, scale) * len(relu)
+    # packed output = split16 row layout of y: [hi | hi | lo | 1 1 0 ...]
+    N = dims[-1]
+    ypc = yp.cpu().float()
+    yc = y.cpu()
+    hi = yc.half().float()
+    assert torch.equal(ypc[:, :N], hi) and torch.equal(ypc[:, N:2 * N], hi)
+    assert torch.equal(ypc[:, 2 * N:3 * N], (yc - hi).half().float())
+    tail = ypc[:, 3 * N:]
+    assert torch.equal(tail[:, :2], torch.ones(rows, 2)) and float(tail[:, 2:].abs().max()) == 0.0
