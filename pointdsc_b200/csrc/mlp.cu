@@ -45,17 +45,34 @@ __device__ __forceinline__ void ml_split_pair(float a, float b, uint32_t& hi, ui
     lo = pack_half2(a - back.x, b - back.y);
 }
 
-__global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p) {
+constexpr uint32_t ML_PITCH = 528;     // bytes between staged rows: 512 + 16, so that row-per-thread LDS.128 are conflict free
+constexpr uint32_t ML_STAGE_BYTES = 128 * ML_PITCH;
+
+// Stages rows [row0, row0 + nrows) of a row-major fp32 [rows, width] matrix into shared memory, one bulk copy per
+// row (whole warp; lane 0 posts the byte count first).
+__device__ __forceinline__ void ml_stage_rows(uint8_t* dst, const float* src, long long row0, int nrows, int width,
+                                              uint64_t* bar, int lane) {
+    if (lane == 0) mbar_arrive_expect_tx(bar, (uint32_t)nrows * (uint32_t)width * 4u);
+    __syncwarp();
+    for (int r = lane; r < nrows; r += 32)
+        bulk_g2s(dst + (uint32_t)r * ML_PITCH, src + (row0 + r) * width, (uint32_t)width * 4u, bar);
+}
+
+__global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     float* bsm = reinterpret_cast<float*>(wsm + p.w_bytes);
-    __shared__ uint64_t w_bar, mma_bar;
+    uint8_t* xs = wsm + p.w_bytes + 1024;                  // staged input rows
+    uint8_t* as = xs + ML_STAGE_BYTES;                     // staged residual rows (only when add_out)
+    __shared__ uint64_t w_bar, mma_bar, x_bar, a_bar;
     __shared__ uint32_t tmem_base_s;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         mbar_init(&w_bar, 1);
         mbar_init(&mma_bar, 1);
+        mbar_init(&x_bar, 1);
+        mbar_init(&a_bar, 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(&tmem_base_s, 256);
@@ -64,7 +81,9 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-    // weights: one bulk copy per CTA (they stay resident while the CTA walks its row tiles)
+    const long long n_tiles = (p.rows + 127) / 128;
+    const int K0 = p.K[0], NL = p.N[p.n_layers - 1];
+    // weights: one bulk copy per CTA (they stay resident while the CTA walks its row tiles); first tile's rows
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(&w_bar, p.w_bytes);
         for (uint32_t off = 0; off < p.w_bytes; off += 32768u) {
@@ -72,26 +91,32 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
             bulk_g2s(wsm + off, p.wpack + off, n, &w_bar);
         }
     }
+    if (warp == 0 && (long long)blockIdx.x < n_tiles) {
+        const long long row0 = (long long)blockIdx.x * 128;
+        const int nrows = (int)min(128LL, p.rows - row0);
+        ml_stage_rows(xs, p.x, row0, nrows, K0, &x_bar, lane);
+        if (p.add_out) ml_stage_rows(as, p.add_out, row0, nrows, NL, &a_bar, lane);
+    }
     for (uint32_t i = threadIdx.x; i < p.n_bias; i += ML_THREADS) bsm[i] = p.bias[i];
     __syncthreads();
     mbar_wait_role(&w_bar, 0);
 
-    uint32_t mma_phase = 0;
-    const long long n_tiles = (p.rows + 127) / 128;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    uint32_t mma_phase = 0, io_phase = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, io_phase ^= 1) {
         const long long row = tile * 128 + threadIdx.x;
         const bool live = row < p.rows;
         const long long rrow = live ? row : p.rows - 1;
-        // ---- input row -> A operand (hi, lo) in TMEM ----
+        const long long next = tile + gridDim.x;
+        // ---- input row (staged in shared memory) -> A operand (hi, lo) in TMEM ----
+        mbar_wait_role(&x_bar, io_phase);
         {
-            const int K0 = p.K[0];
-            const float4* xr = reinterpret_cast<const float4*>(p.x + rrow * K0);
+            const float4* xr = reinterpret_cast<const float4*>(xs + (uint32_t)threadIdx.x * ML_PITCH);
             const float4* ar = p.add_in ? reinterpret_cast<const float4*>(p.add_in + rrow * K0) : nullptr;
             for (int c = 0; c < K0 / 32; ++c) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    float4 v = __ldg(xr + c * 8 + i);
+                    float4 v = xr[c * 8 + i];
                     if (ar) { const float4 a = __ldg(ar + c * 8 + i); v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w; }
                     ml_split_pair(v.x, v.y, hi[2 * i], lo[2 * i]);
                     ml_split_pair(v.z, v.w, hi[2 * i + 1], lo[2 * i + 1]);
@@ -104,7 +129,7 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
             const int K = p.K[l], N = p.N[l];
             tmem_st_wait();
             tc_fence_before();
-            __syncthreads();           // every row's A operand is in TMEM, and everyone is done reading D
+            __syncthreads();           // every row's A operand is in TMEM, and everyone is done reading D (and xs)
             if (warp == 0) {
                 tc_fence_after();
                 const uint32_t idesc = umma_idesc_f16(128, N);
@@ -122,11 +147,15 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
                     }
                 }
                 umma_commit_elect(&mma_bar);
+                // the input stage is free (all rows were read before the barrier above): prefetch the next tile
+                if (l == 0 && next < n_tiles)
+                    ml_stage_rows(xs, p.x, next * 128, (int)min(128LL, p.rows - next * 128), K0, &x_bar, lane);
             }
-            mbar_wait_role(&mma_bar, mma_phase);
+            const bool last = l + 1 == p.n_layers;
+            mbar_wait(&mma_bar, mma_phase);
             mma_phase ^= 1;
             tc_fence_after();
-            const bool last = l + 1 == p.n_layers;
+            if (last && p.add_out) mbar_wait_role(&a_bar, io_phase);
             const float* bias = bsm + p.b_off[l];
             for (int c = 0; c < N / 32; ++c) {
                 uint32_t r[32];
@@ -146,10 +175,10 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
                     tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
                 } else {
                     if (p.add_out) {
-                        const float4* ar = reinterpret_cast<const float4*>(p.add_out + rrow * N + c * 32);
+                        const float4* ar = reinterpret_cast<const float4*>(as + (uint32_t)threadIdx.x * ML_PITCH) + c * 8;
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            const float4 a = __ldg(ar + i);
+                            const float4 a = ar[i];
                             v[4 * i] += a.x; v[4 * i + 1] += a.y; v[4 * i + 2] += a.z; v[4 * i + 3] += a.w;
                         }
                     }
@@ -181,8 +210,10 @@ __global__ void __launch_bounds__(ML_THREADS) mlp_chain_kernel(const MlpParams p
                 }
             }
         }
-        // the next tile's A stores must not overtake this tile's last MMA: it has completed (mma_bar), and D reads
-        // are ordered by the __syncthreads at the top of the next layer loop
+        if (p.add_out && next < n_tiles) {
+            __syncthreads();           // every row of the residual stage has been read
+            if (warp == 0) ml_stage_rows(as, p.add_out, next * 128, (int)min(128LL, p.rows - next * 128), NL, &a_bar, lane);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -207,15 +238,17 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     }
     p.w_bytes = woff; p.n_bias = boff;
     if (y_packed && (Kp % 8 != 0 || Kp < 3 * dims[n_layers] + 8)) { set_error("mlp_chain: bad packed row length %d", Kp); return PDSC_ERR_ARG; }
-    const int smem = (int)(p.w_bytes + p.n_bias * sizeof(float) + 1024);
+    // weights | biases (1 KB slot) | staged input rows | staged residual rows
+    if (p.n_bias * sizeof(float) > 1024) { set_error("mlp_chain: too many bias entries"); return PDSC_ERR_ARG; }
+    const int smem = (int)(p.w_bytes + 1024 + ML_STAGE_BYTES + (add_out ? ML_STAGE_BYTES : 0) + 1024);
+    if (smem > 227 * 1024) { set_error("mlp_chain: chain does not fit in shared memory (%d bytes)", smem); return PDSC_ERR_ARG; }
     static int smem_set = 0;
     if (smem > smem_set) {
         cudaFuncSetAttribute(mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         smem_set = smem;
     }
     const long long n_tiles = (rows + 127) / 128;
-    const int per_sm = smem <= 100 * 1024 ? 2 : 1;                 // TMEM: 256 of 512 columns per CTA
-    long long grid = (long long)num_sms() * per_sm;
+    long long grid = num_sms();
     if (grid > n_tiles) grid = n_tiles;
     mlp_chain_kernel<<<(int)grid, ML_THREADS, smem, st>>>(p);
     count_launches(1);
