@@ -54,6 +54,21 @@ def workload_name(args):
            f"{NUM_LAYERS} layers, C={C}, seeded weights"
 
 
+def ncu_traffic(args):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE attention launch, from the committed ncu --set full
+    capture of the same workload (profiles/r01_ncu_attn_pp.json); None for other workloads."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_attn_pp.json")
+    if not (os.path.exists(path) and args.pairs == 16 and args.n == 5000 and args.mode == "split16"):
+        return None
+    try:
+        d = json.load(open(path))["launches"][0]
+        unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+        rd, wr = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
+        return float(rd["value"]) * unit[rd["unit"]] + float(wr["value"]) * unit[wr["unit"]]
+    except Exception:
+        return None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -297,7 +312,8 @@ def main():
         achieved = flops_per_launch / (avg_attn_ms * 1e-3) / 1e12
         roofline = {"bound": "tensor", "kernel": f"pdsc_nonlocal_attn[{args.mode}]", "achieved": achieved,
                     "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_sustained"],
-                    "traffic": None, "peak_source": pk["source"] + ", bf16 sustained",
+                    "traffic": ncu_traffic(args), "traffic_note": "dram bytes of the main attention kernel per launch (ncu --set full, "
+                    "profiles/r01_ncu_attn_pp.json); algorithmic HBM bytes per launch = 4*B*N*C*4", "peak_source": pk["source"] + ", bf16 sustained",
                     "algorithmic_flops_per_launch": flops_per_launch, "avg_launch_ms": avg_attn_ms,
                     "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms}
         line = {
