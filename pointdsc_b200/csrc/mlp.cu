@@ -48,31 +48,37 @@ __device__ __forceinline__ void ml_split_pair(float a, float b, uint32_t& hi, ui
 constexpr uint32_t ML_PITCH = 528;     // bytes between staged rows: 512 + 16, so that row-per-thread LDS.128 are conflict free
 constexpr uint32_t ML_STAGE_BYTES = 128 * ML_PITCH;
 
-// Stages rows [row0, row0 + nrows) of a row-major fp32 [rows, width] matrix into shared memory, one bulk copy per
-// row (whole warp; lane 0 posts the byte count first).
-__device__ __forceinline__ void ml_stage_rows(uint8_t* dst, const float* src, long long row0, int nrows, int width,
-                                              uint64_t* bar, int lane) {
-    if (lane == 0) mbar_arrive_expect_tx(bar, (uint32_t)nrows * (uint32_t)width * 4u);
-    __syncwarp();
-    for (int r = lane; r < nrows; r += 32)
-        bulk_g2s(dst + (uint32_t)r * ML_PITCH, src + (row0 + r) * width, (uint32_t)width * 4u, bar);
+// Stages rows [row0, row0 + nrows) of a row-major fp32 [rows, width] matrix into shared memory (padded pitch) with
+// 16-byte cp.async copies: global reads are warp-coalesced, completion is tracked per thread in commit groups.
+__device__ __forceinline__ void ml_stage_rows(uint8_t* dst, const float* src, long long row0, int nrows, int width) {
+    const int sh = width == 128 ? 5 : 4;               // log2 of the 16-byte chunks per row (width is 128 or 64)
+    const int total = nrows << sh;
+    const float* base = src + row0 * width;
+#pragma unroll 4
+    for (int idx = threadIdx.x; idx < total; idx += ML_THREADS) {
+        const int r = idx >> sh, c = idx & ((1 << sh) - 1);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst + (uint32_t)r * ML_PITCH + (uint32_t)c * 16u)),
+                     "l"(base + (size_t)r * width + c * 4)
+                     : "memory");
+    }
 }
+__device__ __forceinline__ void ml_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void ml_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     float* bsm = reinterpret_cast<float*>(wsm + p.w_bytes);
     uint8_t* xs = wsm + p.w_bytes + 1024;                  // staged input rows
-    uint8_t* as = xs + ML_STAGE_BYTES;                     // staged residual rows (only when add_out)
-    __shared__ uint64_t w_bar, mma_bar, x_bar, a_bar;
+    uint8_t* as = xs + ML_STAGE_BYTES;                     // staged residual rows (when add_out), then the fp32 output rows
+    __shared__ uint64_t w_bar, mma_bar;
     __shared__ uint32_t tmem_base_s;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         mbar_init(&w_bar, 1);
         mbar_init(&mma_bar, 1);
-        mbar_init(&x_bar, 1);
-        mbar_init(&a_bar, 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(&tmem_base_s, 256);
@@ -91,24 +97,27 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
             bulk_g2s(wsm + off, p.wpack + off, n, &w_bar);
         }
     }
-    if (warp == 0 && (long long)blockIdx.x < n_tiles) {
+    // commit groups per tile, oldest first: X(tile) | A(tile) (residual, only with add_out) | X(next tile) ...
+    {
         const long long row0 = (long long)blockIdx.x * 128;
         const int nrows = (int)min(128LL, p.rows - row0);
-        ml_stage_rows(xs, p.x, row0, nrows, K0, &x_bar, lane);
-        if (p.add_out) ml_stage_rows(as, p.add_out, row0, nrows, NL, &a_bar, lane);
+        ml_stage_rows(xs, p.x, row0, nrows, K0);
+        ml_commit();
+        if (p.add_out) { ml_stage_rows(as, p.add_out, row0, nrows, NL); ml_commit(); }
     }
     for (uint32_t i = threadIdx.x; i < p.n_bias; i += ML_THREADS) bsm[i] = p.bias[i];
     __syncthreads();
     mbar_wait_role(&w_bar, 0);
 
-    uint32_t mma_phase = 0, io_phase = 0;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, io_phase ^= 1) {
+    uint32_t mma_phase = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long row = tile * 128 + threadIdx.x;
         const bool live = row < p.rows;
         const long long rrow = live ? row : p.rows - 1;
         const long long next = tile + gridDim.x;
         // ---- input row (staged in shared memory) -> A operand (hi, lo) in TMEM ----
-        mbar_wait_role(&x_bar, io_phase);
+        if (p.add_out) ml_wait_group<1>(); else ml_wait_group<0>();
+        __syncthreads();               // X(tile) has landed for every thread's copies
         {
             const float4* xr = reinterpret_cast<const float4*>(xs + (uint32_t)threadIdx.x * ML_PITCH);
             const float4* ar = p.add_in ? reinterpret_cast<const float4*>(p.add_in + rrow * K0) : nullptr;
@@ -147,15 +156,17 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                     }
                 }
                 umma_commit_elect(&mma_bar);
+            }
+            if (l == 0) {
                 // the input stage is free (all rows were read before the barrier above): prefetch the next tile
-                if (l == 0 && next < n_tiles)
-                    ml_stage_rows(xs, p.x, next * 128, (int)min(128LL, p.rows - next * 128), K0, &x_bar, lane);
+                if (next < n_tiles) ml_stage_rows(xs, p.x, next * 128, (int)min(128LL, p.rows - next * 128), K0);
+                ml_commit();           // (an empty group when there is no next tile keeps the group count uniform)
             }
             const bool last = l + 1 == p.n_layers;
             mbar_wait(&mma_bar, mma_phase);
             mma_phase ^= 1;
             tc_fence_after();
-            if (last && p.add_out) mbar_wait_role(&a_bar, io_phase);
+            if (last && p.add_out) { ml_wait_group<1>(); __syncthreads(); }   // A(tile) has landed; X(next) may still fly
             const float* bias = bsm + p.b_off[l];
             for (int c = 0; c < N / 32; ++c) {
                 uint32_t r[32];
@@ -174,18 +185,18 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                     tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
                     tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
                 } else {
+                    // residual add in place in the stage; the finished fp32 row leaves through per-row bulk stores
+                    float4* orow = reinterpret_cast<float4*>(as + (uint32_t)threadIdx.x * ML_PITCH) + c * 8;
                     if (p.add_out) {
-                        const float4* ar = reinterpret_cast<const float4*>(as + (uint32_t)threadIdx.x * ML_PITCH) + c * 8;
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            const float4 a = ar[i];
+                            const float4 a = orow[i];
                             v[4 * i] += a.x; v[4 * i + 1] += a.y; v[4 * i + 2] += a.z; v[4 * i + 3] += a.w;
                         }
                     }
-                    if (live && p.y) {
-                        float4* yr = reinterpret_cast<float4*>(p.y + row * N + c * 32);
+                    if (p.y) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) yr[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                        for (int i = 0; i < 8; ++i) orow[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
                     }
                     if (live && p.y_packed) {
                         // row layout of pdsc_split16_rows: [hi(N) | hi(N) | lo(N) | 1 1 0 ..]
@@ -210,11 +221,27 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                 }
             }
         }
-        if (p.add_out && next < n_tiles) {
-            __syncthreads();           // every row of the residual stage has been read
-            if (warp == 0) ml_stage_rows(as, p.add_out, next * 128, (int)min(128LL, p.rows - next * 128), NL, &a_bar, lane);
+        if (p.y || p.add_out) {
+            __syncthreads();                   // every row of the stage is final (and the residual has been consumed)
+            if (p.y) {
+                // stage -> global, warp-coalesced: one instruction writes one whole row
+                const int nrows = (int)min(128LL, p.rows - tile * 128);
+                const int sh = NL == 128 ? 5 : 4, total = nrows << sh;
+                float4* ybase = reinterpret_cast<float4*>(p.y + tile * 128 * NL);
+#pragma unroll 4
+                for (int idx = threadIdx.x; idx < total; idx += ML_THREADS) {
+                    const int r = idx >> sh, c = idx & ((1 << sh) - 1);
+                    ybase[idx] = *reinterpret_cast<const float4*>(as + (uint32_t)r * ML_PITCH + (uint32_t)c * 16u);
+                }
+                __syncthreads();               // the stage has been read
+            }
+            if (p.add_out) {
+                if (next < n_tiles) ml_stage_rows(as, p.add_out, next * 128, (int)min(128LL, p.rows - next * 128), NL);
+                ml_commit();
+            }
         }
     }
+    ml_wait_group<0>();
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 256);
@@ -240,7 +267,7 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     if (y_packed && (Kp % 8 != 0 || Kp < 3 * dims[n_layers] + 8)) { set_error("mlp_chain: bad packed row length %d", Kp); return PDSC_ERR_ARG; }
     // weights | biases (1 KB slot) | staged input rows | staged residual rows
     if (p.n_bias * sizeof(float) > 1024) { set_error("mlp_chain: too many bias entries"); return PDSC_ERR_ARG; }
-    const int smem = (int)(p.w_bytes + 1024 + ML_STAGE_BYTES + (add_out ? ML_STAGE_BYTES : 0) + 1024);
+    const int smem = (int)(p.w_bytes + 1024 + ML_STAGE_BYTES + ((add_out || y) ? ML_STAGE_BYTES : 0) + 1024);
     if (smem > 227 * 1024) { set_error("mlp_chain: chain does not fit in shared memory (%d bytes)", smem); return PDSC_ERR_ARG; }
     static int smem_set = 0;
     if (smem > smem_set) {
