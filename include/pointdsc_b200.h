@@ -69,6 +69,19 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
                        int B, int N, int C, float sigma_spat, int mode,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Fused q/k/v projection + operand packing, and the attention on operands packed that way.
+ *  pdsc_qkv_pack replaces projection_q/k/v of NonLocalBlock.forward (models/PointDSC.py:29-37): from the layer input
+ *  x [B,N,C] fp32 it computes q = x Wq + bq, k, v on the tensor cores (fp16 hi/lo split, fp32 accumulation) and writes
+ *  them into `ws` directly as the fp16 hi/lo operand tiles of the attention kernel (V already transposed), together
+ *  with the sigma-normalised key points.  wpack (device): the tcgen05 operand images of Wq, Wk, Wv (layout as for
+ *  pdsc_mlp_chain, 64 KB each); bias (device): bq|bk|bv fp32 [3C].  C must be 128.
+ *  pdsc_nonlocal_attn_packed then produces the message [B,N,C] from `ws` (same ws, B, N, C; workspace size from
+ *  pdsc_workspace_bytes(PDSC_OP_NONLOCAL_ATTN, ...)); mode PDSC_ATTN_SPLIT16 or PDSC_ATTN_FP16. */
+int pdsc_qkv_pack(const float* x, const void* wpack, const float* bias, const float* src, const float* tgt,
+                  int B, int N, int C, float sigma_spat, void* ws, size_t ws_bytes, void* stream);
+int pdsc_nonlocal_attn_packed(float* out, int64_t ld_out, int B, int N, int C, int mode,
+                              void* ws, size_t ws_bytes, void* stream);
+
 /* Operand packing for the channel-last 1x1-conv GEMMs of NonLocalNet / NonLocalBlock
  *  (models/PointDSC.py:12-23,54-62; the GEMMs themselves stay torch/cuBLAS calls).
  *  v = x (+ add) (then ReLU if relu != 0), x/add/y_out fp32 [rows,K]; y_out (nullable) receives v;

@@ -40,6 +40,9 @@ SIGNATURES = {
     "pdsc_post_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
                                  c_void_p]),
     "pdsc_split16_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    "pdsc_qkv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_size_t,
+                              c_void_p]),
+    "pdsc_nonlocal_attn_packed": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "pdsc_mlp_chain": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_int, c_void_p]),
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
@@ -171,6 +174,32 @@ def split16_rows(x, add=None, relu=False, y_out=None, out16=None):
     _check(rc, "pdsc_split16_rows")
     _count()
     return out16
+
+
+def qkv_pack(x, wpack, bias, src, tgt, sigma_spat, ws=None, mode=ATTN_SPLIT16):
+    """x [B,N,128] fp32 -> attention operand tiles in the workspace (q/k/v projections fused with the packing).
+    wpack = cat(pack_umma_b(Wq^T), pack_umma_b(Wk^T), pack_umma_b(Wv^T)); bias = cat(bq, bk, bv).  Returns the
+    workspace tensor to hand to nonlocal_attn_packed."""
+    lib = load()
+    B, N, C = x.shape
+    w = _ws(workspace_bytes(OP_NONLOCAL_ATTN, B, N, C, mode=mode), x.device, ws)
+    rc = lib.pdsc_qkv_pack(_ptr(x, torch.float32, "x"), _ptr(wpack, torch.uint8, "wpack"), _ptr(bias, torch.float32, "bias"),
+                           _ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"), B, N, C, float(sigma_spat),
+                           w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_qkv_pack")
+    _count()
+    return w
+
+
+def nonlocal_attn_packed(w, B, N, C, mode=ATTN_SPLIT16, out=None):
+    """Message [B,N,C] from operand tiles prepared by qkv_pack in workspace tensor `w`."""
+    lib = load()
+    if out is None:
+        out = torch.empty(B, N, C, dtype=torch.float32, device=w.device)
+    rc = lib.pdsc_nonlocal_attn_packed(_ptr(out, torch.float32, "out"), C, B, N, C, mode, w.data_ptr(), w.numel(), _stream())
+    _check(rc, "pdsc_nonlocal_attn_packed")
+    _count()
+    return out
 
 
 class MlpChain:

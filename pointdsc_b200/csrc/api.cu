@@ -107,6 +107,24 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
     return PDSC_ERR_ARG;
 }
 
+int pdsc_qkv_pack(const float* x, const void* wpack, const float* bias, const float* src, const float* tgt, int B, int N,
+                  int C, float sigma_spat, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(x && wpack && bias && src && tgt && ws, "qkv_pack: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0, "qkv_pack: bad shape B=%d N=%d", B, N);
+    PDSC_REQUIRE(aligned16(x) && aligned16(wpack), "qkv_pack: x and wpack must be 16-byte aligned");
+    PDSC_REQUIRE(sigma_spat > 0.f, "qkv_pack: sigma_spat must be positive");
+    return launch_qkv_pack(x, wpack, bias, src, tgt, B, N, C, sigma_spat, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_nonlocal_attn_packed(float* out, int64_t ld_out, int B, int N, int C, int mode, void* ws, size_t ws_bytes,
+                              void* stream) {
+    PDSC_REQUIRE(out && ws, "nonlocal_attn_packed: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0, "nonlocal_attn_packed: bad shape B=%d N=%d", B, N);
+    PDSC_REQUIRE(ld_out >= C && ld_out % 4 == 0 && aligned16(out), "nonlocal_attn_packed: bad output stride/alignment");
+    PDSC_REQUIRE(mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16, "nonlocal_attn_packed: mode must be SPLIT16 or FP16");
+    return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_layers, const int32_t* dims,
                    const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y_out,
                    void* y_packed, int Kp, void* stream) {

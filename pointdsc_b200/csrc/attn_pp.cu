@@ -35,7 +35,7 @@ constexpr int PP_C = 128;                 // channels (head dim)
 constexpr int PP_SUB = 128;               // rows per sub-tile
 constexpr int PP_BM = 2 * PP_SUB;         // query rows per CTA
 constexpr int PP_BN = 64;                 // keys per tile
-constexpr uint32_t PP_QTILE_BYTES = 65536;   // per 128 rows: hi row-linear [128][64 words] | lo 2 swizzled blocks [128 rows x 128 B]
+constexpr uint32_t PP_QTILE_BYTES = 65536;   // per 128 rows: hi blk(ch 0-63) | hi blk(ch 64-127) | lo blk | lo blk, 16 KB swizzled blocks [128 rows x 128 B]
 constexpr uint32_t PP_QLO_OFF = 32768;
 constexpr uint32_t PP_QLO_BYTES = 32768;
 constexpr uint32_t PP_KTILE_BYTES = 32768;   // per 64 keys: hi blk(ch 0-63) | hi blk(ch 64-127) | lo blk | lo blk, 8 KB each
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(256) attn_pp_prep_kernel(const float* __restri
         }
         uint4 hi, lo;
         pp_split8(xq, hi, lo);
-        *reinterpret_cast<uint4*>(qd + r * 256 + c8 * 16) = hi;
+        *reinterpret_cast<uint4*>(qd + (uint32_t)(c8 >> 3) * 16384u + pp_swz(r, c8 & 7)) = hi;
         *reinterpret_cast<uint4*>(qd + PP_QLO_OFF + (uint32_t)(c8 >> 3) * 16384u + pp_swz(r, c8 & 7)) = lo;
         pp_split8(xk, hi, lo);
         uint8_t* kt = kd + (size_t)(r >> 6) * PP_KTILE_BYTES + (uint32_t)(c8 >> 3) * PP_KBLK_BYTES + pp_swz(r & 63, c8 & 7);
@@ -502,11 +502,11 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             const int qrow = min(grow, N - 1);
             // ---- Q_hi rows -> TMEM (this thread: 32 of the 64 words of its row) ----
             {
-                const uint4* qsrc = reinterpret_cast<const uint4*>(p.Qw + q128 * PP_QTILE_BYTES + (size_t)row * 256 + half * 128);
+                const uint8_t* qsrc = p.Qw + q128 * PP_QTILE_BYTES + (size_t)half * 16384u;   // block `half` = channels 64 half ..
                 uint32_t r[32];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const uint4 v4 = __ldg(qsrc + i);
+                    const uint4 v4 = __ldg(reinterpret_cast<const uint4*>(qsrc + pp_swz((uint32_t)row, (uint32_t)i)));
                     r[4 * i] = v4.x; r[4 * i + 1] = v4.y; r[4 * i + 2] = v4.z; r[4 * i + 3] = v4.w;
                 }
                 tmem_st_h32<32>(q_x, r);
@@ -759,9 +759,15 @@ static PpLayout pp_layout(int B, int N) {
 
 size_t attn_pp_workspace(int B, int N) { return pp_layout(B, N).total; }
 
-int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
-                   float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
-                   size_t ws_bytes, cudaStream_t st) {
+void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw) {
+    const PpLayout L = pp_layout(B, N);
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+    *Qw = base + L.q; *Kw = base + L.k; *Vw = base + L.v;
+    *Pw = reinterpret_cast<float*>(base + L.pts);
+}
+
+// Main kernel on operand tiles already present in the workspace (written by attn_pp_prep_kernel or qkv_pack_kernel).
+int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mode, void* ws, size_t ws_bytes, cudaStream_t st) {
     if (C != PP_C) { set_error("nonlocal_attn: C=%d unsupported (kernels are built for C=%d)", C, PP_C); return PDSC_ERR_ARG; }
     const PpLayout L = pp_layout(B, N);
     if (!ws || ws_bytes < L.total) {
@@ -792,16 +798,11 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
     const int smem_bytes = (int)sizeof(PpSmem) + 1024;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(attn_pp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
         cudaFuncSetAttribute(attn_pp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         attr_set = true;
     }
     const int G = pp_grid(B, NRB, NT);
     cudaMemsetAsync(p.counters, 0, (size_t)B * NRB * 2 * sizeof(int), st);
-    const float qscale = 1.4426950408889634f / sqrtf((float)C);
-    attn_pp_prep_kernel<<<dim3(2 * NRB, B), 256, 128 * 129 * 4, st>>>(
-        q, k, v, ld, src, tgt, N, 2 * NRB, qscale, 1.0f / sigma_spat, const_cast<uint8_t*>(p.Qw), const_cast<uint8_t*>(p.Kw),
-        const_cast<uint8_t*>(p.Vw), const_cast<float*>(p.Pw));
     p.trace = nullptr;
     const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
     if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
@@ -821,8 +822,33 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
         }
         cudaFree(p.trace);
     }
-    count_launches(2);
+    count_launches(1);
     return check_launch("nonlocal_attn(tcgen05 ping-pong)");
+}
+
+int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
+                   float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
+                   size_t ws_bytes, cudaStream_t st) {
+    if (C != PP_C) { set_error("nonlocal_attn: C=%d unsupported (kernels are built for C=%d)", C, PP_C); return PDSC_ERR_ARG; }
+    const PpLayout L = pp_layout(B, N);
+    if (!ws || ws_bytes < L.total) {
+        set_error("nonlocal_attn: workspace too small (%zu < %zu)", ws_bytes, L.total);
+        return PDSC_ERR_WORKSPACE;
+    }
+    const int NRB = (N + PP_BM - 1) / PP_BM;
+    uint8_t *Qw, *Kw, *Vw;
+    float* Pw;
+    attn_pp_tile_pointers(ws, B, N, &Qw, &Kw, &Vw, &Pw);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(attn_pp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
+        attr_set = true;
+    }
+    const float qscale = 1.4426950408889634f / sqrtf((float)C);
+    attn_pp_prep_kernel<<<dim3(2 * NRB, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, 2 * NRB, qscale, 1.0f / sigma_spat,
+                                                                      Qw, Kw, Vw, Pw);
+    count_launches(1);
+    return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, st);
 }
 
 }  // namespace pdsc

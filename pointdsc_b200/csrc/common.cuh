@@ -204,6 +204,9 @@ size_t attn_pp_workspace(int B, int N);
 int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
                    float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
                    size_t ws_bytes, cudaStream_t st);
+int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mode, void* ws, size_t ws_bytes, cudaStream_t st);
+int launch_qkv_pack(const float* y, const void* wpack, const float* bias, const float* src, const float* tgt, int B, int N,
+                    int C, float sigma_spat, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin,
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st);
 int launch_split16_rows(const float* x, const float* add, float* y_out, void* out16, long long rows, int K, int Kp,

@@ -165,6 +165,8 @@ class PointDSC(nn.Module):
                     # fused on-chip chains (pdsc_mlp_chain): PointCN conv+BN+ReLU, and fc_message + residual
                     L["pcn_chain"] = _cabi.MlpChain([L["pcn"]], [True])
                     L["msg_chain"] = _cabi.MlpChain([L["m0"], L["m3"], L["m6"]], [True, True, False])
+                    L["qkv_w"] = torch.cat([_cabi.pack_umma_b(Wq), _cabi.pack_umma_b(Wk), _cabi.pack_umma_b(Wv)]).contiguous()
+                    L["qkv_b"] = torch.cat([bq, bk, bv]).float().contiguous()
             layers.append(L)
         P["layers"] = layers
         P["cls"] = [_fold(self.classification[i], None) for i in (0, 2, 4)]
@@ -211,14 +213,22 @@ class PointDSC(nn.Module):
         return feat.view(B, N, C)
 
     def _encode_fused(self, P, feat, src, tgt, B, N, C):
-        """Per layer: one fused kernel for PointCN (writes y1 and its packed fp16 hi/lo rows), one library GEMM for
-        the fused q/k/v projection, the attention kernel, one fused kernel for fc_message + residual."""
+        """Per layer four kernels, all hand-written: PointCN (pdsc_mlp_chain), q/k/v projection straight into the
+        attention operand tiles (pdsc_qkv_pack), the attention itself, fc_message + residual (pdsc_mlp_chain)."""
         x = feat
+        if self.attn_mode == _cabi.ATTN_FP32:
+            for L in P["layers"]:
+                y1, y1p = _cabi.mlp_chain(x, L["pcn_chain"], want_y=True, want_packed=True)
+                qkv = torch.mm(y1p, L["qkv_s"], out_dtype=torch.float32).view(B, N, 3 * C)
+                msg = _cabi.nonlocal_attn(qkv[:, :, 0:C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:3 * C], src, tgt,
+                                          P["sigma_spat"], mode=self.attn_mode, ws=self._ws)
+                x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)
+            return x.view(B, N, C)
         for L in P["layers"]:
-            y1, y1p = _cabi.mlp_chain(x, L["pcn_chain"], want_y=True, want_packed=True)     # PointCN conv+BN+ReLU
-            qkv = torch.mm(y1p, L["qkv_s"], out_dtype=torch.float32).view(B, N, 3 * C)
-            msg = _cabi.nonlocal_attn(qkv[:, :, 0:C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:3 * C], src, tgt,
-                                      P["sigma_spat"], mode=self.attn_mode, ws=self._ws)
+            y1, _ = _cabi.mlp_chain(x, L["pcn_chain"])                                      # PointCN conv+BN+ReLU
+            w = _cabi.qkv_pack(y1.view(B, N, C), L["qkv_w"], L["qkv_b"], src, tgt, P["sigma_spat"], ws=self._ws,
+                               mode=self.attn_mode)
+            msg = _cabi.nonlocal_attn_packed(w, B, N, C, mode=self.attn_mode)
             x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)          # feat + fc_message(msg)
         return x.view(B, N, C)
 
