@@ -88,10 +88,10 @@ __global__ void __launch_bounds__(HY_THREADS) seed_hypo_kernel(
     __shared__ HypoSmem sm;
     const int kp = (k + 3) & ~3;        // rows padded to a multiple of 4
     const int ldf = C + 4;              // feature row stride (floats), keeps float4 alignment
-    const int ldm = HY_MAXK + 1;
+    const int ldm = kp + 1;             // odd row stride: conflict-free column walks
     float* F = dyn;                     // [kp][ldf]
     float* M = F + (size_t)kp * ldf;    // [k][ldm]
-    float* V = M + (size_t)HY_MAXK * ldm;   // [T+1][HY_MAXK]
+    float* V = M + (size_t)kp * ldm;    // [T+1][HY_MAXK]
     const int row_id = blockIdx.x;      // b*S + s
     const int b = row_id / S;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -254,7 +254,7 @@ int launch_seed_hypotheses(const float* normed, const float* src, const float* t
     float* iterates = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + align_up(sizeof(unsigned int) * (size_t)B, 256));
     cudaMemsetAsync(mask, 0, sizeof(unsigned int) * (size_t)B, st);
     const int kp = (k + 3) & ~3;
-    const size_t smem = sizeof(float) * ((size_t)kp * (C + 4) + (size_t)HY_MAXK * (HY_MAXK + 1) +
+    const size_t smem = sizeof(float) * ((size_t)kp * (C + 4) + (size_t)kp * (kp + 1) +
                                          (size_t)(num_iterations + 1) * HY_MAXK);
     if (smem > 200 * 1024) { set_error("seed_hypotheses: C=%d too large for shared memory", C); return PDSC_ERR_ARG; }
     cudaFuncSetAttribute(seed_hypo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
