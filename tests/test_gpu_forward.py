@@ -65,9 +65,9 @@ def test_batched_forward_equals_per_pair_runs():
 
 
 @pytest.mark.parametrize("mode", MODES)
-@pytest.mark.parametrize("fam,N", [("3dmatch", 5000), ("kitti", 10000)])
+@pytest.mark.parametrize("fam,N", [("3dmatch", 5000), ("kitti", 10000), ("kitti", 50000)])
 def test_full_size_properties(fam, N, mode):
-    """BASELINE configs 2/3 at full size: the registration recovers the synthetic ground-truth
+    """BASELINE configs 2/3/4 at full size (N=50000: the single-very-large-pair case, run through the whole forward): the registration recovers the synthetic ground-truth
     motion, labels are consistent with the returned initial transform, permuting the
     correspondences permutes the labels and leaves the transform (nearly) unchanged."""
     cfg = synth.CONFIGS[fam]
