@@ -25,6 +25,7 @@
 #include "sm100.cuh"
 
 #include <math.h>
+#include <algorithm>
 #include <stdlib.h>
 
 namespace pdsc {
@@ -49,6 +50,7 @@ constexpr uint32_t PP_PTS_BYTES = PP_PTS_FLOATS * 4;
 constexpr float PP_RESCALE_LOG2 = 8.0f;      // lazy rescale threshold (log2 units)
 constexpr uint32_t PT_S = 0, PT_O = 128, PT_Q = 384;
 constexpr int PP_SOFT_WARPS = 16;
+constexpr int PP_DEFAULT_CLUSTER = 1;                  // CTAs per cluster unless PDSC_ATTN_CLUSTER says otherwise
 constexpr int PP_THREADS = (PP_SOFT_WARPS + 4) * 32;   // + one warpgroup of role warps (producer, MMA issuer, 2 idle)
 
 struct PpSmem {
@@ -305,9 +307,11 @@ struct PpParams {
     float* out; int64_t ld_out;
     float* part_o;          // [grid][2 slots][2 sub-tiles][128 rows][128 ch]
     float* part_ml;         // [grid][2][2][128][2]  (m, l)
-    int* counters;          // [B * NRB][2]
-    int N, NRB, NT;         // rows, 256-row blocks per pair, 64-key tiles per pair
-    long long total_steps;  // B * NRB * NT
+    int* counters;          // [B * NRBp][2]
+    int N, NT;              // rows, 64-key tiles per pair
+    int NRBp;               // 256-row blocks per pair rounded up to even: tile / counter indexing
+    int NU;                 // work units per pair: 256-row blocks (no cluster) or 512-row block pairs (cluster of 2)
+    long long total_steps;  // B * NU * NT
     int qk_terms, pv_terms, dbg;   // hi/lo product terms issued per contraction
     long long* trace;       // optional timeline of CTA 0 (PDSC_ATTN_TRACE): trace[step * 16 + event] = SM clock
 };
@@ -342,6 +346,11 @@ __device__ __forceinline__ float4 pp_ldcg4(const float* p) {
 // ------------------------------------------------------------------------------------------------
 // Main kernel.
 // ------------------------------------------------------------------------------------------------
+// CL = CTAs per cluster.  CL == 2: the two CTAs of a cluster walk the same key tiles of one pair for two neighbouring
+// 256-row blocks; each loads HALF of every K / V^T tile and multicasts it to both (cp.async.bulk .multicast::cluster),
+// which halves the L2 -> SM traffic; a stage is released by both MMA issuers (multicast tcgen05.commit).
+// DBG: instantiation with the timing-experiment knobs (PDSC_ATTN_DBG) and the timeline trace compiled in.
+template <int CL, bool DBG>
 __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p) {
     constexpr int NP = 16;                   // key pairs per thread per tile (32 keys)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -349,16 +358,19 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
     PpSmem& sm = *reinterpret_cast<PpSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
     __shared__ int last_flag[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int G = gridDim.x, cta = blockIdx.x;
+    const int G = gridDim.x / CL, cta = blockIdx.x;        // G work ranges; range index = cluster index
+    const int rank = CL == 1 ? 0 : (int)cluster_ctarank();
+    const int rng = blockIdx.x / CL;
     const int NT = p.NT;
-    const long long lo = pp_range_lo(p.total_steps, cta, G), hi = pp_range_lo(p.total_steps, cta + 1, G);
-    const bool tracing = p.trace != nullptr && cta == 0 && lane == 0;
+    const long long lo = pp_range_lo(p.total_steps, rng, G), hi = pp_range_lo(p.total_steps, rng + 1, G);
+    const bool tracing = DBG && p.trace != nullptr && cta == 0 && lane == 0;
+    constexpr uint16_t CL_MASK = (uint16_t)((1u << CL) - 1u);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             mbar_init(&sm.q_full[i], PP_SOFT_WARPS / 2 + 1);
-            mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], 1);
-            mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], 1);
+            mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], CL);     // released by the MMA issuer of every CTA in the cluster
+            mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], CL);
             mbar_init(&sm.pts_full[i], 1); mbar_init(&sm.pts_empty[i], PP_SOFT_WARPS);
             mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], PP_SOFT_WARPS / 2); mbar_init(&sm.pv_done[i], 1);
         }
@@ -368,6 +380,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
     if (warp == PP_SOFT_WARPS + 1) tmem_alloc(&sm.tmem_base, 512);
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();            // every CTA's barriers exist before a peer signals them
     tc_fence_after();
     // The allocation is the whole 512-column TMEM of the SM (one CTA per SM), so its base is column 0, lane 0:
     // every TMEM address below is a compile-time constant.
@@ -385,9 +398,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             PpSeg s;
             uint32_t kt = 0;
             for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
-                const int b = s.blk / p.NRB, rb = s.blk - b * p.NRB;
-                const size_t q128 = (size_t)b * (2 * p.NRB) + 2 * rb;      // first 128-row tile of the block
-                const size_t kt0 = (size_t)b * (4 * p.NRB);                // first 64-key tile of the pair
+                const int b = s.blk / p.NU, rb = (s.blk - b * p.NU) * CL + rank;
+                const size_t q128 = (size_t)b * (2 * p.NRBp) + 2 * rb;     // first 128-row tile of the block
+                const size_t kt0 = (size_t)b * (4 * p.NRBp);               // first 64-key tile of the pair
                 if (si > 0) mbar_wait_role(&sm.q_free, (si - 1) & 1);      // all MMAs of the previous segment are done
                 for (int x = 0; x < 2; ++x) {
                     mbar_arrive_expect_tx(&sm.q_full[x], PP_QLO_BYTES);
@@ -398,14 +411,24 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     const uint32_t par = ((kt >> 1) - 1) & 1;               // previous use of this stage
                     if (kt >= 2) mbar_wait_role(&sm.k_empty[st], par);
                     mbar_arrive_expect_tx(&sm.k_full[st], PP_KTILE_BYTES);
-                    bulk_g2s(sm.k[st], p.Kw + (kt0 + j) * PP_KTILE_BYTES, PP_KTILE_BYTES, &sm.k_full[st]);
+                    if (CL == 1) {
+                        bulk_g2s(sm.k[st], p.Kw + (kt0 + j) * PP_KTILE_BYTES, PP_KTILE_BYTES, &sm.k_full[st]);
+                    } else {
+                        constexpr uint32_t part = PP_KTILE_BYTES / CL;
+                        bulk_g2s_multicast(sm.k[st] + rank * part, p.Kw + (kt0 + j) * PP_KTILE_BYTES + rank * part, part, &sm.k_full[st], CL_MASK);
+                    }
                     PP_TRACE(kt, 0);
                     if (kt >= 2) mbar_wait_role(&sm.pts_empty[st], par);
                     mbar_arrive_expect_tx(&sm.pts_full[st], PP_PTS_BYTES);
                     bulk_g2s(sm.pts[st], p.Pw + (kt0 + j) * PP_PTS_FLOATS, PP_PTS_BYTES, &sm.pts_full[st]);
                     if (kt >= 2) mbar_wait_role(&sm.v_empty[st], par);
                     mbar_arrive_expect_tx(&sm.v_full[st], PP_VTILE_BYTES);
-                    bulk_g2s(sm.v[st], p.Vw + (kt0 + j) * PP_VTILE_BYTES, PP_VTILE_BYTES, &sm.v_full[st]);
+                    if (CL == 1) {
+                        bulk_g2s(sm.v[st], p.Vw + (kt0 + j) * PP_VTILE_BYTES, PP_VTILE_BYTES, &sm.v_full[st]);
+                    } else {
+                        constexpr uint32_t part = PP_VTILE_BYTES / CL;
+                        bulk_g2s_multicast(sm.v[st] + rank * part, p.Vw + (kt0 + j) * PP_VTILE_BYTES + rank * part, part, &sm.v_full[st], CL_MASK);
+                    }
                     PP_TRACE(kt, 1);
                 }
             }
@@ -436,7 +459,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 tc_fence_after();
                 pp_issue_qk<1>(q_desc1, kd, qk_terms);
                 umma_commit_elect(&sm.s_full[1]);
-                umma_commit_elect(&sm.k_empty[kt & 1]);
+                if (CL == 1) umma_commit_elect(&sm.k_empty[kt & 1]); else umma_commit_elect_multicast(&sm.k_empty[kt & 1], CL_MASK);
             }
             for (int t = 0; t < n; ++t, ++kt) {
                 const int st = kt & 1, nx = st ^ 1;
@@ -465,11 +488,11 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 tc_fence_after();
                 pp_issue_pv<1>(vd, pv_terms, acc);
                 umma_commit_elect(&sm.pv_done[1]);
-                umma_commit_elect(&sm.v_empty[st]);
+                if (CL == 1) umma_commit_elect(&sm.v_empty[st]); else umma_commit_elect_multicast(&sm.v_empty[st], CL_MASK);
                 if (more) {
                     pp_issue_qk<1>(q_desc1, kd, qk_terms);
                     umma_commit_elect(&sm.s_full[1]);
-                    umma_commit_elect(&sm.k_empty[nx]);
+                    if (CL == 1) umma_commit_elect(&sm.k_empty[nx]); else umma_commit_elect_multicast(&sm.k_empty[nx], CL_MASK);
                 }
                 PP_TRACE(kt, 5);
             }
@@ -488,16 +511,16 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const uint32_t o_x = tmem + lane_addr + PT_O + 128u * x;
         const uint32_t q_x = tmem + lane_addr + PT_Q + 64u * x;
         const int kp0 = half * NP;                    // first key pair of this thread inside a tile
-        const int dbg = p.dbg;
+        const int dbg = DBG ? p.dbg : 0;
         const bool pv3 = p.pv_terms > 2;
         const int N = p.N;
         long long pos = lo;
         PpSeg s;
         uint32_t kt = 0;
         for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
-            const int b = s.blk / p.NRB, rb = s.blk - b * p.NRB;
-            const size_t q128 = (size_t)b * (2 * p.NRB) + 2 * rb + x;
-            const size_t kt0 = (size_t)b * (4 * p.NRB);
+            const int b = s.blk / p.NU, rb = (s.blk - b * p.NU) * CL + rank;
+            const size_t q128 = (size_t)b * (2 * p.NRBp) + 2 * rb + x;
+            const size_t kt0 = (size_t)b * (4 * p.NRBp);
             const int grow = (2 * rb + x) * PP_SUB + row;
             const int qrow = min(grow, N - 1);
             // ---- Q_hi rows -> TMEM (this thread: 32 of the 64 words of its row) ----
@@ -530,7 +553,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 // compatibilities of this thread's row against its 32 keys (needs only the points)
                 float2 e[NP];
                 mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1);
-                if (dbg & 1) {
+                // (the never-taken constant branch also fences the compat block: without it ptxas spreads the
+                // compat arithmetic over the following waits and the kernel runs ~6% slower)
+                if (DBG ? (dbg & 1) : (N < 0)) {
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = make_float2(0.5f, 0.25f);
                 } else {
@@ -658,7 +683,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 }
             } else {
                 // partial: store (O, m, l); the last contributor of the block combines all partials
-                const size_t base = ((size_t)(cta * 2 + (si == 0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                const size_t base = ((size_t)(cta * 2 + (si == 0 ? 0 : 1)) * 2 + x) * PP_SUB + row;      // cta = rng * CL + rank
                 float* po = p.part_o + base * PP_C + half * 64;
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
@@ -675,7 +700,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 }
                 __threadfence();
                 named_bar_sync(1 + x, 256);
-                if ((warp & 7) == 0 && lane == 0) last_flag[x] = atomicAdd(&p.counters[s.blk * 2 + x], 1);
+                if ((warp & 7) == 0 && lane == 0) last_flag[x] = atomicAdd(&p.counters[((size_t)b * p.NRBp + rb) * 2 + x], 1);
                 named_bar_sync(1 + x, 256);
                 const long long T = p.total_steps, x0 = (long long)s.blk * NT;
                 const int c_first = (int)(((x0 + 1) * G + T - 1) / T) - 1;
@@ -684,12 +709,12 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     __threadfence();
                     float M = -INFINITY;
                     for (int c = c_first; c <= c_last; ++c) {
-                        const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                        const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
                         M = fmaxf(M, pp_ldcg(p.part_ml + idx * 2));
                     }
                     float L = 0.f;
                     for (int c = c_first; c <= c_last; ++c) {
-                        const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                        const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
                         L += exp2f(pp_ldcg(p.part_ml + idx * 2) - M) * pp_ldcg(p.part_ml + idx * 2 + 1);
                     }
                     const float inv_l = 1.0f / L;
@@ -700,7 +725,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
 #pragma unroll
                         for (int i = 0; i < 16; ++i) acc[i] = 0.f;
                         for (int c = c_first; c <= c_last; ++c) {
-                            const size_t idx = ((size_t)(c * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
+                            const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
                             const float f = exp2f(pp_ldcg(p.part_ml + idx * 2) - M);
                             const float* src_o = p.part_o + idx * PP_C + half * 64 + ch;
 #pragma unroll
@@ -721,17 +746,45 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
     }
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();            // the peer may still signal this CTA's barriers until it is done too
     if (warp == PP_SOFT_WARPS + 1) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
-static int pp_grid(int B, int NRB, int NT) {
-    const long long total = (long long)B * NRB * NT;
+// PDSC_ATTN_CLUSTER (read per call; tuning knob): CTAs per cluster, 1 or 2.
+static int pp_cluster() {
+    const char* e = getenv("PDSC_ATTN_CLUSTER");
+    const int c = e ? atoi(e) : PP_DEFAULT_CLUSTER;
+    return c == 2 ? 2 : 1;
+}
+
+static int pp_smem_bytes() { return (int)sizeof(PpSmem) + 1024; }
+
+// clusters of 2 that can be resident at once (one CTA per SM; both CTAs of a cluster sit in one GPC)
+static int pp_max_clusters() {
+    static int cached = -1;
+    if (cached >= 0) return cached;
+    cudaFuncSetAttribute(attn_pp_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, pp_smem_bytes());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * num_sms()); cfg.blockDim = dim3(PP_THREADS); cfg.dynamicSmemBytes = pp_smem_bytes();
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, attn_pp_kernel<2, false>, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = num_sms() / 2; }
+    cached = n;
+    return n;
+}
+
+// number of work ranges (= CTAs without clusters, = clusters with them)
+static int pp_grid(int B, int NU, int NT, int CL) {
+    const long long total = (long long)B * NU * NT;
     // PDSC_ATTN_GRID (read per call; a test/tuning knob): unset = one CTA per SM (stream-K),
-    // 0 = one CTA per 256-row block (no partials), n = n CTAs
+    // 0 = one range per work unit (no partials), n = n ranges
     const char* e = getenv("PDSC_ATTN_GRID");
     const int knob = e ? atoi(e) : -1;
-    long long g = knob < 0 ? num_sms() : (knob == 0 ? (long long)B * NRB : knob);
+    long long g = knob < 0 ? (CL == 1 ? num_sms() : pp_max_clusters()) : (knob == 0 ? (long long)B * NU : knob);
     if (g > total) g = total;
     if (g < 1) g = 1;
     return (int)g;
@@ -742,8 +795,10 @@ struct PpLayout {
 };
 static PpLayout pp_layout(int B, int N) {
     const int NRB = (N + PP_BM - 1) / PP_BM, NT = (N + PP_BN - 1) / PP_BN;
-    const size_t t128 = (size_t)B * 2 * NRB;
-    const size_t G = (size_t)pp_grid(B, NRB, NT);
+    const int NRBp = (NRB + 1) & ~1;
+    const size_t t128 = (size_t)B * 2 * NRBp;
+    // partial slots for the larger of the two launch shapes, so the layout does not depend on the cluster knob
+    const size_t G = (size_t)std::max(pp_grid(B, NRB, NT, 1), 2 * pp_grid(B, NRBp / 2, NT, 2));
     PpLayout L;
     size_t off = 0;
     L.q = off; off += t128 * PP_QTILE_BYTES;
@@ -752,12 +807,13 @@ static PpLayout pp_layout(int B, int N) {
     L.pts = off; off += align_up(t128 * 2 * PP_PTS_BYTES, 1024);
     L.part_o = off; off += G * 2 * 2 * PP_SUB * PP_C * sizeof(float);
     L.part_ml = off; off += G * 2 * 2 * PP_SUB * 2 * sizeof(float);
-    L.counters = off; off += align_up((size_t)B * NRB * 2 * sizeof(int), 1024);
+    L.counters = off; off += align_up((size_t)B * NRBp * 2 * sizeof(int), 1024);
     L.total = off + 1024;
     return L;
 }
 
 size_t attn_pp_workspace(int B, int N) { return pp_layout(B, N).total; }
+int attn_pp_tiles128(int N) { return 2 * ((((N + PP_BM - 1) / PP_BM) + 1) & ~1); }   // 128-row tiles per pair in the workspace
 
 void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw) {
     const PpLayout L = pp_layout(B, N);
@@ -783,8 +839,11 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.part_o = reinterpret_cast<float*>(base + L.part_o);
     p.part_ml = reinterpret_cast<float*>(base + L.part_ml);
     p.counters = reinterpret_cast<int*>(base + L.counters);
-    p.N = N; p.NRB = NRB; p.NT = NT;
-    p.total_steps = (long long)B * NRB * NT;
+    const int CL = pp_cluster();
+    const int NRBp = (NRB + 1) & ~1;
+    p.N = N; p.NT = NT; p.NRBp = NRBp;
+    p.NU = CL == 1 ? NRB : NRBp / 2;
+    p.total_steps = (long long)B * p.NU * NT;
     // PDSC_ATTN_SPLIT16: all three hi/lo terms for both contractions.  PDSC_ATTN_PV_TERMS=2 (tuning knob) drops
     // the P_lo V_hi term and takes the row sum over the rounded P_hi: ~2e-4 relative message error.
     // PDSC_ATTN_FP16: hi*hi only.
@@ -795,18 +854,32 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     if (dbg < 0) { const char* e = getenv("PDSC_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
     p.dbg = dbg;
     if (dbg & 4) p.qk_terms = p.pv_terms = 0;       // no MMAs
-    const int smem_bytes = (int)sizeof(PpSmem) + 1024;
+    const int smem_bytes = pp_smem_bytes();
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(attn_pp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(attn_pp_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(attn_pp_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(attn_pp_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         attr_set = true;
     }
-    const int G = pp_grid(B, NRB, NT);
-    cudaMemsetAsync(p.counters, 0, (size_t)B * NRB * 2 * sizeof(int), st);
+    const int G = pp_grid(B, p.NU, NT, CL);
+    cudaMemsetAsync(p.counters, 0, (size_t)B * NRBp * 2 * sizeof(int), st);
     p.trace = nullptr;
     const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
     if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
-    attn_pp_kernel<<<G, PP_THREADS, smem_bytes, st>>>(p);
+    if (CL == 1 && (dbg || trace_path)) {
+        attn_pp_kernel<1, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+    } else if (CL == 1) {
+        attn_pp_kernel<1, false><<<G, PP_THREADS, smem_bytes, st>>>(p);
+    } else {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * G); cfg.blockDim = dim3(PP_THREADS); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, attn_pp_kernel<2, false>, p);
+    }
     if (trace_path) {
         static long long h[16 * 256];
         cudaDeviceSynchronize();
@@ -835,7 +908,7 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
         set_error("nonlocal_attn: workspace too small (%zu < %zu)", ws_bytes, L.total);
         return PDSC_ERR_WORKSPACE;
     }
-    const int NRB = (N + PP_BM - 1) / PP_BM;
+    const int NT128 = attn_pp_tiles128(N);
     uint8_t *Qw, *Kw, *Vw;
     float* Pw;
     attn_pp_tile_pointers(ws, B, N, &Qw, &Kw, &Vw, &Pw);
@@ -845,7 +918,7 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
         attr_set = true;
     }
     const float qscale = 1.4426950408889634f / sqrtf((float)C);
-    attn_pp_prep_kernel<<<dim3(2 * NRB, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, 2 * NRB, qscale, 1.0f / sigma_spat,
+    attn_pp_prep_kernel<<<dim3(NT128, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, NT128, qscale, 1.0f / sigma_spat,
                                                                       Qw, Kw, Vw, Pw);
     count_launches(1);
     return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, st);

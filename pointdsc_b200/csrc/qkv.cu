@@ -22,6 +22,7 @@ namespace pdsc {
 using namespace sm100;
 
 void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw);   // attn_pp.cu
+int attn_pp_tiles128(int N);
 
 constexpr int QK_THREADS = 256;       // two independent 4-warp groups per CTA (even / odd tiles) sharing the weights
 constexpr uint32_t QK_BLK = 16384;        // one operand block: 128 rows x 64 fp16, 128-byte rows, 128B swizzle
@@ -212,7 +213,7 @@ int launch_qkv_pack(const float* y, const void* wpack, const float* bias, const 
     QkvParams p;
     p.y = y; p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.src = src; p.tgt = tgt;
     attn_pp_tile_pointers(ws, B, N, &p.Qw, &p.Kw, &p.Vw, &p.Pw);
-    p.B = B; p.N = N; p.NT128 = 2 * ((N + 255) / 256);
+    p.B = B; p.N = N; p.NT128 = attn_pp_tiles128(N);
     p.qscale = 1.4426950408889634f / sqrtf((float)C);
     p.inv_sigma = 1.0f / sigma_spat;
     const int smem = (int)(3 * QK_IMG + 1024);   // weights + one operand/image buffer per warp group

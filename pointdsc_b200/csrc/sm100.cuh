@@ -64,10 +64,14 @@ __device__ __forceinline__ void mbar_wait_role(uint64_t* bar, uint32_t parity) {
 // in uniform registers, which is what tcgen05.mma operands want).
 __device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
+        "{\n\t.reg .pred p, q;\n\t.reg .u32 spin;\n\t"
+        "mov.u32 spin, 0;\n\t"
         "WAIT_LOOP_%=:\n\t"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra WAIT_DONE_%=;\n\t"
+        "add.u32 spin, spin, 1;\n\t"
+        "setp.gt.u32 q, spin, 4194304;\n\t"      // a mis-programmed pipeline traps instead of hanging the GPU
+        "@q trap;\n\t"
         "bra WAIT_LOOP_%=;\n\t"
         "WAIT_DONE_%=:\n\t}"
         ::"r"(smem_u32(bar)), "r"(parity), "r"(20000u)
@@ -80,6 +84,24 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
                      smem_u32(smem_dst)),
                  "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+
+// same, delivered to the same shared-memory offset (and signalling the same-offset mbarrier) in every CTA of `cta_mask`
+__device__ __forceinline__ void bulk_g2s_multicast(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "h"(cta_mask)
+                 : "memory");
+}
+// ---- thread-block clusters ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {      // every thread of every CTA in the cluster
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 // ---- bulk async copy shared -> global (TMA engine), bulk-group completion ---------------------------
@@ -167,6 +189,15 @@ __device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
         "{\n\t.reg .pred pe;\n\t"
         "elect.sync _|pe, 0xffffffff;\n\t"
         "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+// commit that arrives on the same-offset mbarrier of every CTA in `cta_mask` (whole warp executes, elected lane issues)
+__device__ __forceinline__ void umma_commit_elect_multicast(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile(
+        "{\n\t.reg .pred pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+        "h"(cta_mask)
+        : "memory");
 }
 // Arrives on the mbarrier when all previously issued tcgen05 async ops of this thread complete.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
