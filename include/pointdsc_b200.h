@@ -40,6 +40,10 @@ extern "C" {
 #define PDSC_ATTN_FP16 2       /* tcgen05 single-pass fp16 (fast, outside the parity tolerance) */
 
 /* operations for pdsc_workspace_bytes */
+/* distance form of pdsc_nn_match */
+#define PDSC_MATCH_DOT 0       /* sqrt(2 - 2 a.b + 1e-6)       (datasets/LidarFeatureExtractor.py:110) */
+#define PDSC_MATCH_L2 1        /* sqrt(max(|a|^2+|b|^2-2 a.b, 1e-30))  (algorithms/matching.py:29-30)  */
+
 #define PDSC_OP_NONLOCAL_ATTN 1
 #define PDSC_OP_PICK_SEEDS 2
 #define PDSC_OP_SEED_KNN 3
@@ -177,6 +181,35 @@ int pdsc_power_normalize(const float* y, float* v_inout, int N, int32_t* converg
 int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N,
                          float sigma_spat, int num_iterations, int32_t* iters_out,
                          void* ws, size_t ws_bytes, void* stream);
+
+/* ---- next rows: the callers either side of the forward -------------------------------------------- */
+
+/* (N2) nearest neighbour in descriptor space; replaces find_nn algorithms/matching.py:22-65 and the
+ *  argmin of datasets/LidarFeatureExtractor.py:110-111.  A fp32 [P,Na,D], B fp32 [P,Nb,D] (P independent problems,
+ *  D <= 64).  idx1 int64 [P,Na]: index of the nearest B row (ties -> lowest index, like np.argmin / torch.min);
+ *  idx2 (nullable): the second nearest (the reference masks the first and takes the min again, :35-37);
+ *  val1 / val2 (nullable) fp32: the two distances, so a caller can see how close a decision was. */
+int pdsc_nn_match(const float* A, const float* B, int P, int Na, int Nb, int D, int metric,
+                  int64_t* idx1, int64_t* idx2, float* val1, float* val2, void* stream);
+
+/* (N2) mutual check + compaction; replaces datasets/LidarFeatureExtractor.py:112-117 and nn_to_mutual /
+ *  torch_intersect algorithms/matching.py:67-87,225-242.  idx_ab int64 [P,Na] (A -> B), idx_ba int64 [P,Nb]
+ *  (B -> A; may be NULL when use_mutual == 0).  corr int64 [P,Na,2] receives the kept (i, idx_ab[i]) pairs in
+ *  ascending i, count int32 [P] how many. */
+int pdsc_mutual_corr(const int64_t* idx_ab, const int64_t* idx_ba, int P, int Na, int Nb, int use_mutual,
+                     int64_t* corr, int32_t* count, void* stream);
+
+/* (N3) registration metrics; replaces the per-pair loop of TransformationLoss.forward libs/loss.py:34-63.
+ *  trans, gt_trans fp32 [P,4,4]; src, tgt fp32 [P,N,3].  out fp32 [P,4] = rotation error [deg], translation error
+ *  [cm] (the reference's x100), mean |T src - tgt|, mean |T src - tgt|^2. */
+int pdsc_registration_metrics(const float* trans, const float* gt_trans, const float* src, const float* tgt,
+                              int P, int N, float* out, void* stream);
+
+/* (N3) inlier classification statistics; replaces the sklearn calls of ClassificationLoss.forward
+ *  libs/loss.py:96-112.  pred, gt fp32 [P,N]; predicted label = pred > thr, true label = gt != 0.
+ *  counts int32 [P,4] = tp, fp, fn, tn; sums fp32 [P,2] = sum pred*gt, sum pred*(1-gt). */
+int pdsc_classification_counts(const float* pred, const float* gt, int P, int N, float thr,
+                               int32_t* counts, float* sums, void* stream);
 
 #ifdef __cplusplus
 }

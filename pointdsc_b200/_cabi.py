@@ -43,6 +43,11 @@ SIGNATURES = {
     "pdsc_qkv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_size_t,
                               c_void_p]),
     "pdsc_nonlocal_attn_packed": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
+    "pdsc_nn_match": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                              c_void_p]),
+    "pdsc_mutual_corr": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "pdsc_registration_metrics": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "pdsc_classification_counts": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pdsc_mlp_chain": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_int, c_void_p]),
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
@@ -362,3 +367,63 @@ def power_iter_full(src, tgt, sigma_spat, num_iterations, ws=None):
     _check(rc, "pdsc_power_iter_full")
     _count()
     return v, iters
+
+
+MATCH_DOT, MATCH_L2 = 0, 1
+
+
+def nn_match(A, B, metric=MATCH_L2, want_second=False, want_values=False):
+    """A [P,Na,D], B [P,Nb,D] fp32 -> idx1 int64 [P,Na] (nearest B row per A row, ties to the lowest index), plus
+    idx2 (second nearest) and the two distances when asked for (pdsc_nn_match)."""
+    lib = load()
+    P, Na, D = A.shape
+    Nb = B.shape[1]
+    dev = A.device
+    idx1 = torch.empty(P, Na, dtype=torch.int64, device=dev)
+    idx2 = torch.empty(P, Na, dtype=torch.int64, device=dev) if want_second else None
+    v1 = torch.empty(P, Na, dtype=torch.float32, device=dev) if want_values else None
+    v2 = torch.empty(P, Na, dtype=torch.float32, device=dev) if want_values else None
+    rc = lib.pdsc_nn_match(_ptr(A, torch.float32, "A"), _ptr(B, torch.float32, "B"), P, Na, Nb, D, metric, idx1.data_ptr(),
+                           idx2.data_ptr() if idx2 is not None else None, v1.data_ptr() if v1 is not None else None,
+                           v2.data_ptr() if v2 is not None else None, _stream())
+    _check(rc, "pdsc_nn_match")
+    _count()
+    return idx1, idx2, v1, v2
+
+
+def mutual_corr(idx_ab, idx_ba, Nb, use_mutual=True):
+    """idx_ab int64 [P,Na], idx_ba int64 [P,Nb] -> (corr int64 [P,Na,2], count int32 [P]); rows [0,count) are valid."""
+    lib = load()
+    P, Na = idx_ab.shape
+    corr = torch.empty(P, Na, 2, dtype=torch.int64, device=idx_ab.device)
+    count = torch.empty(P, dtype=torch.int32, device=idx_ab.device)
+    rc = lib.pdsc_mutual_corr(_ptr(idx_ab, torch.int64, "idx_ab"), _ptr(idx_ba, torch.int64, "idx_ba") if idx_ba is not None else None,
+                              P, Na, Nb, 1 if use_mutual else 0, corr.data_ptr(), count.data_ptr(), _stream())
+    _check(rc, "pdsc_mutual_corr")
+    _count()
+    return corr, count
+
+
+def registration_metrics(trans, gt_trans, src, tgt):
+    """[P,4,4] x2, [P,N,3] x2 -> fp32 [P,4] = RE [deg], TE [cm], mean residual, mean squared residual."""
+    lib = load()
+    P, N, _ = src.shape
+    out = torch.empty(P, 4, dtype=torch.float32, device=src.device)
+    rc = lib.pdsc_registration_metrics(_ptr(trans, torch.float32, "trans"), _ptr(gt_trans, torch.float32, "gt_trans"),
+                                       _ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"), P, N, out.data_ptr(), _stream())
+    _check(rc, "pdsc_registration_metrics")
+    _count()
+    return out
+
+
+def classification_counts(pred, gt, thr=0.0):
+    """pred, gt fp32 [P,N] -> (int32 [P,4] tp fp fn tn, fp32 [P,2] sum pred*gt, sum pred*(1-gt))."""
+    lib = load()
+    P, N = pred.shape
+    counts = torch.empty(P, 4, dtype=torch.int32, device=pred.device)
+    sums = torch.empty(P, 2, dtype=torch.float32, device=pred.device)
+    rc = lib.pdsc_classification_counts(_ptr(pred, torch.float32, "pred"), _ptr(gt, torch.float32, "gt"), P, N, float(thr),
+                                        counts.data_ptr(), sums.data_ptr(), _stream())
+    _check(rc, "pdsc_classification_counts")
+    _count()
+    return counts, sums

@@ -125,6 +125,36 @@ int pdsc_nonlocal_attn_packed(float* out, int64_t ld_out, int B, int N, int C, i
     return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int pdsc_nn_match(const float* A, const float* B, int P, int Na, int Nb, int D, int metric, int64_t* idx1, int64_t* idx2,
+                  float* val1, float* val2, void* stream) {
+    PDSC_REQUIRE(A && B && idx1, "nn_match: null pointer");
+    PDSC_REQUIRE(P > 0 && Na > 0 && Nb > 0 && D > 0, "nn_match: bad shape P=%d Na=%d Nb=%d D=%d", P, Na, Nb, D);
+    PDSC_REQUIRE(P <= 65535, "nn_match: at most 65535 problems per call");
+    PDSC_REQUIRE(metric == PDSC_MATCH_DOT || metric == PDSC_MATCH_L2, "nn_match: unknown metric %d", metric);
+    return launch_nn_match(A, B, P, Na, Nb, D, metric, idx1, idx2, val1, val2, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_mutual_corr(const int64_t* idx_ab, const int64_t* idx_ba, int P, int Na, int Nb, int use_mutual, int64_t* corr,
+                     int32_t* count, void* stream) {
+    PDSC_REQUIRE(idx_ab && corr && count && (idx_ba || !use_mutual), "mutual_corr: null pointer");
+    PDSC_REQUIRE(P > 0 && Na > 0 && Nb > 0, "mutual_corr: bad shape P=%d Na=%d Nb=%d", P, Na, Nb);
+    return launch_mutual_corr(idx_ab, idx_ba, P, Na, Nb, use_mutual, corr, count, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_registration_metrics(const float* trans, const float* gt_trans, const float* src, const float* tgt, int P, int N,
+                              float* out, void* stream) {
+    PDSC_REQUIRE(trans && gt_trans && src && tgt && out, "registration_metrics: null pointer");
+    PDSC_REQUIRE(P > 0 && N > 0, "registration_metrics: bad shape P=%d N=%d", P, N);
+    return launch_registration_metrics(trans, gt_trans, src, tgt, P, N, out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_classification_counts(const float* pred, const float* gt, int P, int N, float thr, int32_t* counts, float* sums,
+                               void* stream) {
+    PDSC_REQUIRE(pred && gt && counts && sums, "classification_counts: null pointer");
+    PDSC_REQUIRE(P > 0 && N > 0, "classification_counts: bad shape P=%d N=%d", P, N);
+    return launch_classification_counts(pred, gt, P, N, thr, counts, sums, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_layers, const int32_t* dims,
                    const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y_out,
                    void* y_packed, int Kp, void* stream) {

@@ -200,6 +200,14 @@ int launch_attn_fp32(const float* q, const float* k, const float* v, int64_t ld,
 int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
                    float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
                    size_t ws_bytes, cudaStream_t st);
+int launch_nn_match(const float* A, const float* Bm, int P, int Na, int Nb, int D, int metric, int64_t* idx1, int64_t* idx2,
+                    float* val1, float* val2, cudaStream_t st);
+int launch_mutual_corr(const int64_t* idx_ab, const int64_t* idx_ba, int P, int Na, int Nb, int use_mutual, int64_t* corr,
+                       int32_t* count, cudaStream_t st);
+int launch_registration_metrics(const float* trans, const float* gt, const float* src, const float* tgt, int P, int N, float* out,
+                                cudaStream_t st);
+int launch_classification_counts(const float* pred, const float* gt, int P, int N, float thr, int32_t* counts, float* sums,
+                                 cudaStream_t st);
 size_t attn_pp_workspace(int B, int N);
 int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
                    float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
