@@ -4,7 +4,7 @@
 //   algorithms/matching.py:22-65 (find_nn)      |a|^2 + |b|^2 - 2 a.b, clamp, sqrt, argmin (+ second nearest)
 //   algorithms/matching.py:225-242 (nn_to_mutual) + torch_intersect :67-87
 //
-// nn_match_kernel: one thread per query row (descriptor in registers), reference rows staged through shared
+// nn_match_kernel: two query rows per thread (descriptors in registers), reference rows staged through shared
 // memory in tiles and read as broadcasts; every (query, reference) dot product is ONE sequential fp32 FMA chain
 // over the channels, so the A->B and the B->A pass see bit-identical values (the mutual check relies on that).
 // Ties go to the lower index, like np.argmin / torch.min.  HBM traffic is the two descriptor sets (L2-resident
@@ -14,17 +14,19 @@
 
 namespace pdsc {
 
-constexpr int NM_THREADS = 128;      // query rows per CTA
+constexpr int NM_THREADS = 128;
+constexpr int NM_ROWS = 2;           // query rows per thread (NM_THREADS * NM_ROWS per CTA)
 constexpr int NM_TILE = 64;          // reference rows per shared-memory tile
 
-// value the reference takes the argmin of, evaluated with the reference's own rounding steps
-__device__ __forceinline__ float nm_key(float dot, float na, float nb, int metric) {
-    if (metric == PDSC_MATCH_DOT) {
-        // np.sqrt(2 - 2 * dot + 1e-6): the product by 2 is exact, then two rounded additions, then sqrt
-        return __fsqrt_rn(__fadd_rn(__fsub_rn(2.0f, 2.0f * dot), 1e-6f));
-    }
-    // (|a|^2 + |b|^2) - 2 dot, clamp_min(1e-30), sqrt
-    return __fsqrt_rn(fmaxf(__fsub_rn(__fadd_rn(na, nb), 2.0f * dot), 1e-30f));
+// The reference takes the argmin of sqrt(u) with
+//   u = (2 - 2 dot) + 1e-6                        (np.sqrt(2 - 2 * dot + 1e-6): exact product, two rounded additions)
+//   u = max((|a|^2 + |b|^2) - 2 dot, 1e-30)       (find_nn: clamp_min then sqrt)
+// evaluated with exactly these rounding steps.  sqrt is monotone, so a candidate with u >= the current value can
+// never win; only the rare candidate with a smaller u pays for the correctly rounded sqrt, which decides (two
+// different u can round to the same distance, and then the lower index keeps the place, as in the reference).
+__device__ __forceinline__ float nm_presqrt(float dot, float na, float nb, int metric) {
+    if (metric == PDSC_MATCH_DOT) return __fadd_rn(__fsub_rn(2.0f, 2.0f * dot), 1e-6f);
+    return fmaxf(__fsub_rn(__fadd_rn(na, nb), 2.0f * dot), 1e-30f);
 }
 
 template <int DPAD>
@@ -37,17 +39,27 @@ __global__ void __launch_bounds__(NM_THREADS) nn_match_kernel(const float* __res
     const int p = blockIdx.y;                           // problem (registration pair)
     A += (size_t)p * Na * D;
     Bm += (size_t)p * Nb * D;
-    const int i = blockIdx.x * NM_THREADS + threadIdx.x;
-    const int ic = min(i, Na - 1);
-    float a[DPAD];
-    float na = 0.f;
+    // NM_ROWS query rows per thread: every broadcast LDS.128 of a reference row feeds 4 * NM_ROWS FMAs (the
+    // shared-memory pipe is per SM; at one row per thread it, not the FMA pipe, sets the pace)
+    float a[NM_ROWS][DPAD];
+    float na[NM_ROWS];
+    int row[NM_ROWS];
 #pragma unroll
-    for (int c = 0; c < DPAD; ++c) {
-        a[c] = c < D ? A[(size_t)ic * D + c] : 0.f;
-        na = fmaf(a[c], a[c], na);
+    for (int q = 0; q < NM_ROWS; ++q) {
+        row[q] = (blockIdx.x * NM_ROWS + q) * NM_THREADS + threadIdx.x;
+        const int ic = min(row[q], Na - 1);
+        na[q] = 0.f;
+#pragma unroll
+        for (int c = 0; c < DPAD; ++c) {
+            a[q][c] = c < D ? A[(size_t)ic * D + c] : 0.f;
+            na[q] = fmaf(a[q][c], a[q][c], na[q]);
+        }
     }
-    float best = INFINITY, second = INFINITY;
-    int ibest = 0, isecond = 0;
+    // the two smallest distances so far, their pre-sqrt values and indices
+    float best[NM_ROWS], second[NM_ROWS], best_u[NM_ROWS], second_u[NM_ROWS];
+    int ibest[NM_ROWS], isecond[NM_ROWS];
+#pragma unroll
+    for (int q = 0; q < NM_ROWS; ++q) { best[q] = second[q] = best_u[q] = second_u[q] = INFINITY; ibest[q] = isecond[q] = 0; }
     for (int j0 = 0; j0 < Nb; j0 += NM_TILE) {
         const int nj = min(NM_TILE, Nb - j0);
         __syncthreads();
@@ -63,35 +75,54 @@ __global__ void __launch_bounds__(NM_THREADS) nn_match_kernel(const float* __res
         }
         __syncthreads();
         for (int r = 0; r < nj; r += 4) {
-            float d[4] = {0.f, 0.f, 0.f, 0.f};
+            float d[NM_ROWS][4];
+#pragma unroll
+            for (int q = 0; q < NM_ROWS; ++q)
+#pragma unroll
+                for (int u = 0; u < 4; ++u) d[q][u] = 0.f;
 #pragma unroll
             for (int c = 0; c < DPAD; c += 4) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const float4 b = *reinterpret_cast<const float4*>(&tile[(r + u) * DPAD + c]);   // rows past nj are zero
-                    d[u] = fmaf(a[c], b.x, d[u]);
-                    d[u] = fmaf(a[c + 1], b.y, d[u]);
-                    d[u] = fmaf(a[c + 2], b.z, d[u]);
-                    d[u] = fmaf(a[c + 3], b.w, d[u]);
+#pragma unroll
+                    for (int q = 0; q < NM_ROWS; ++q) {
+                        d[q][u] = fmaf(a[q][c], b.x, d[q][u]);
+                        d[q][u] = fmaf(a[q][c + 1], b.y, d[q][u]);
+                        d[q][u] = fmaf(a[q][c + 2], b.z, d[q][u]);
+                        d[q][u] = fmaf(a[q][c + 3], b.w, d[q][u]);
+                    }
                 }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                if (r + u < nj) {
-                    const float v = nm_key(d[u], na, tnorm[r + u], metric);
-                    const int j = j0 + r + u;
-                    if (v < best) { second = best; isecond = ibest; best = v; ibest = j; }
-                    else if (v < second) { second = v; isecond = j; }
+                const float nb = tnorm[r + u];
+#pragma unroll
+                for (int q = 0; q < NM_ROWS; ++q) {
+                    const float uu = nm_presqrt(d[q][u], na[q], nb, metric);
+                    if (uu < second_u[q] && r + u < nj) {
+                        const float v = __fsqrt_rn(uu);
+                        const int j = j0 + r + u;
+                        if (v < best[q]) {
+                            second[q] = best[q]; isecond[q] = ibest[q]; second_u[q] = best_u[q];
+                            best[q] = v; ibest[q] = j; best_u[q] = uu;
+                        } else if (v < second[q]) {
+                            second[q] = v; isecond[q] = j; second_u[q] = uu;
+                        }
+                    }
                 }
             }
         }
     }
-    if (i < Na) {
-        const size_t o = (size_t)p * Na + i;
-        idx1[o] = ibest;
-        if (idx2) idx2[o] = isecond;
-        if (val1) val1[o] = best;
-        if (val2) val2[o] = second;
+#pragma unroll
+    for (int q = 0; q < NM_ROWS; ++q) {
+        if (row[q] < Na) {
+            const size_t o = (size_t)p * Na + row[q];
+            idx1[o] = ibest[q];
+            if (idx2) idx2[o] = isecond[q];
+            if (val1) val1[o] = best[q];
+            if (val2) val2[o] = second[q];
+        }
     }
 }
 
@@ -141,7 +172,7 @@ __global__ void __launch_bounds__(1024) mutual_corr_kernel(const int64_t* __rest
 
 int launch_nn_match(const float* A, const float* Bm, int P, int Na, int Nb, int D, int metric, int64_t* idx1, int64_t* idx2,
                     float* val1, float* val2, cudaStream_t st) {
-    const dim3 grid((Na + NM_THREADS - 1) / NM_THREADS, P);
+    const dim3 grid((Na + NM_THREADS * NM_ROWS - 1) / (NM_THREADS * NM_ROWS), P);
     if (D <= 32) nn_match_kernel<32><<<grid, NM_THREADS, 0, st>>>(A, Bm, Na, Nb, D, metric, idx1, idx2, val1, val2);
     else if (D <= 36) nn_match_kernel<36><<<grid, NM_THREADS, 0, st>>>(A, Bm, Na, Nb, D, metric, idx1, idx2, val1, val2);
     else if (D <= 64) nn_match_kernel<64><<<grid, NM_THREADS, 0, st>>>(A, Bm, Na, Nb, D, metric, idx1, idx2, val1, val2);
