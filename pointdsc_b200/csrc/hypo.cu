@@ -199,31 +199,36 @@ __global__ void __launch_bounds__(HY_THREADS) seed_hypo_kernel(
         __syncwarp();
     }
     if (lane == 0 && notconv) atomicOr(notconv_mask + b, notconv);
-    if (iterates) {
-        float* itp = iterates + (size_t)row_id * T * k;
-        for (int i = lane; i < T * k; i += 32) itp[i] = V[(size_t)(i / k + 1) * HY_MAXK + (i % k)];
-    }
-    seed_kabsch_warp(V + (size_t)T * HY_MAXK, sm.src, sm.tgt, k, seed_trans + (size_t)row_id * 16,
-                     weights ? weights + (size_t)row_id * k : nullptr);
+    // every iterate goes out: which one the reference ends on is only known once all seeds of the pair have voted
+    // (seed_kabsch_kernel).  The Kabsch step itself (a serial double-precision 3x3 Jacobi, ~40k clk on one lane) is
+    // NOT done here, where it would pin this CTA's 30 KB of shared memory to a single busy lane.
+    float* itp = iterates + (size_t)row_id * T * k;
+    for (int i = lane; i < T * k; i += 32) itp[i] = V[(size_t)(i / k + 1) * HY_MAXK + (i % k)];
 }
 
-// Early-stop fix-up.  stop = first iteration at which every seed of the pair had converged.
-__global__ void __launch_bounds__(32) seed_hypo_fixup_kernel(const float* __restrict__ src,
-                                                             const float* __restrict__ tgt,
-                                                             const int64_t* __restrict__ knn_idx, int N, int S, int k,
-                                                             int T, const float* __restrict__ iterates,
-                                                             const unsigned int* __restrict__ notconv_mask,
-                                                             float* __restrict__ seed_trans,
-                                                             float* __restrict__ weights,
-                                                             int32_t* __restrict__ iters_out) {
-    __shared__ float ps[HY_MAXK][3], pt[HY_MAXK][3];
-    const int row_id = blockIdx.x;
+// Weighted Kabsch of every seed from the iterate the reference stops on: stop = first iteration at which every seed of
+// the pair had converged (models/PointDSC.py:349-356 tests allclose over the whole [S,k] tensor).  One warp per seed,
+// HY_KABSCH_WARPS seeds per CTA, so that ~64 of the serial Jacobi solves are in flight per SM.
+constexpr int HY_KABSCH_WARPS = 4;
+__global__ void __launch_bounds__(32 * HY_KABSCH_WARPS) seed_kabsch_kernel(const float* __restrict__ src,
+                                                                           const float* __restrict__ tgt,
+                                                                           const int64_t* __restrict__ knn_idx, int N, int S, int k,
+                                                                           int T, int n_seeds, const float* __restrict__ iterates,
+                                                                           const unsigned int* __restrict__ notconv_mask,
+                                                                           float* __restrict__ seed_trans,
+                                                                           float* __restrict__ weights,
+                                                                           int32_t* __restrict__ iters_out) {
+    __shared__ float ps_all[HY_KABSCH_WARPS][HY_MAXK][3], pt_all[HY_KABSCH_WARPS][HY_MAXK][3];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row_id = blockIdx.x * HY_KABSCH_WARPS + warp;
+    if (row_id >= n_seeds) return;
+    float (*ps)[3] = ps_all[warp];
+    float (*pt)[3] = pt_all[warp];
     const int b = row_id / S;
     const unsigned int conv = ~notconv_mask[b] & ((T >= 32) ? 0xffffffffu : ((1u << T) - 1u));
     const int used = conv ? (__ffs(conv)) : T;   // iterations actually run by the reference
-    if (iters_out && row_id % S == 0 && threadIdx.x == 0) iters_out[b] = used;
-    if (used == T) return;
-    for (int r = threadIdx.x; r < k; r += 32) {
+    if (iters_out && row_id % S == 0 && lane == 0) iters_out[b] = used;
+    for (int r = lane; r < k; r += 32) {
         const int j = (int)knn_idx[(size_t)row_id * k + r];
         for (int d = 0; d < 3; ++d) {
             ps[r][d] = src[((size_t)b * N + j) * 3 + d];
@@ -262,8 +267,8 @@ int launch_seed_hypotheses(const float* normed, const float* src, const float* t
     const float sig2_feat = sigma * sigma, sig2_spat = sigma_spat * sigma_spat;
     seed_hypo_kernel<<<B * S, HY_THREADS, smem, st>>>(normed, src, tgt, knn_idx, N, C, S, k, sig2_feat, sig2_spat,
                                                       num_iterations, seed_trans, weights, iterates, mask);
-    seed_hypo_fixup_kernel<<<B * S, 32, 0, st>>>(src, tgt, knn_idx, N, S, k, num_iterations, iterates, mask,
-                                                 seed_trans, weights, iters);
+    seed_kabsch_kernel<<<(B * S + HY_KABSCH_WARPS - 1) / HY_KABSCH_WARPS, 32 * HY_KABSCH_WARPS, 0, st>>>(
+        src, tgt, knn_idx, N, S, k, num_iterations, B * S, iterates, mask, seed_trans, weights, iters);
     count_launches(2);
     return check_launch("seed_hypotheses");
 }
