@@ -163,15 +163,18 @@ int launch_pick_seeds(const float* src, const float* scores, int B, int N, float
 
 // ------------------------------------------------------------------------------------------
 // seed kNN, stage 1: D[b][s][j] = 2 - 2 <f_seed(s), f_j>  (self -> +inf), fp32 FMA GEMM
-// tile: 32 seeds x 128 candidates per block, 4x4 outputs per thread, channels in chunks of 32
+// CTA tile 64 seeds x 256 candidates, 8 x 8 outputs per thread, channels in chunks of 32.  Both operands stay
+// row-major in shared memory ([row][channel], pitch 36): a thread reads 4 consecutive channels of a row with one
+// LDS.128 (seed rows: warp-wide broadcast; candidate rows tx + 32 j: conflict free), i.e. 4 LDS.128 per 64 FMAs,
+// and every dot product is one sequential FMA chain over the channels.
 // ------------------------------------------------------------------------------------------
-constexpr int KG_TS = 32, KG_TJ = 128, KG_TC = 32, KG_THREADS = 256;
+constexpr int KG_TS = 64, KG_TJ = 256, KG_TC = 32, KG_THREADS = 256, KG_PITCH = KG_TC + 4;
 
-__global__ void __launch_bounds__(KG_THREADS) knn_dist_kernel(const float* __restrict__ feat,
-                                                              const int64_t* __restrict__ seeds, int N, int C, int S,
-                                                              float* __restrict__ D) {
-    __shared__ __align__(16) float As[KG_TC][KG_TS + 4];
-    __shared__ __align__(16) float Bs[KG_TC][KG_TJ + 4];
+__global__ void __launch_bounds__(KG_THREADS, 2) knn_dist_kernel(const float* __restrict__ feat,
+                                                                 const int64_t* __restrict__ seeds, int N, int C, int S,
+                                                                 float* __restrict__ D) {
+    __shared__ __align__(16) float As[KG_TS * KG_PITCH];
+    __shared__ __align__(16) float Bs[KG_TJ * KG_PITCH];
     __shared__ int seed_idx[KG_TS];
     const int b = blockIdx.z;
     const int s0 = blockIdx.y * KG_TS, j0 = blockIdx.x * KG_TJ;
@@ -181,56 +184,60 @@ __global__ void __launch_bounds__(KG_THREADS) knn_dist_kernel(const float* __res
         seed_idx[threadIdx.x] = s < S ? (int)seeds[(size_t)b * S + s] : -1;
     }
     __syncthreads();
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // tx: 4 candidates, ty: 4 seeds
-    float acc[4][4] = {};
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // seeds ty*8 + i, candidates tx + 32 j
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
     for (int c0 = 0; c0 < C; c0 += KG_TC) {
-        {   // A: 32 seeds x 32 channels = 256 float4 -> one per thread
-            const int r = threadIdx.x >> 3, c4 = threadIdx.x & 7;
+#pragma unroll
+        for (int rep = 0; rep < KG_TS * (KG_TC / 4) / KG_THREADS; ++rep) {   // A: 64 seeds x 8 float4
+            const int f = threadIdx.x + rep * KG_THREADS;
+            const int r = f >> 3, c4 = f & 7;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             const int si = seed_idx[r];
             if (si >= 0) v = *reinterpret_cast<const float4*>(fb + (size_t)si * C + c0 + c4 * 4);
-            As[c4 * 4 + 0][r] = v.x; As[c4 * 4 + 1][r] = v.y; As[c4 * 4 + 2][r] = v.z; As[c4 * 4 + 3][r] = v.w;
+            *reinterpret_cast<float4*>(&As[r * KG_PITCH + c4 * 4]) = v;
         }
 #pragma unroll
-        for (int rep = 0; rep < 4; ++rep) {   // B: 128 candidates x 32 channels = 1024 float4
+        for (int rep = 0; rep < KG_TJ * (KG_TC / 4) / KG_THREADS; ++rep) {   // B: 256 candidates x 8 float4
             const int f = threadIdx.x + rep * KG_THREADS;
             const int r = f >> 3, c4 = f & 7;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (j0 + r < N) v = *reinterpret_cast<const float4*>(fb + (size_t)(j0 + r) * C + c0 + c4 * 4);
-            Bs[c4 * 4 + 0][r] = v.x; Bs[c4 * 4 + 1][r] = v.y; Bs[c4 * 4 + 2][r] = v.z; Bs[c4 * 4 + 3][r] = v.w;
+            *reinterpret_cast<float4*>(&Bs[r * KG_PITCH + c4 * 4]) = v;
         }
         __syncthreads();
+#pragma unroll 1
+        for (int c = 0; c < KG_TC; c += 4) {
+            float4 a[8];
 #pragma unroll
-        for (int c = 0; c < KG_TC; ++c) {
-            const float4 a = *reinterpret_cast<const float4*>(&As[c][ty * 4]);
-            const float4 bq = *reinterpret_cast<const float4*>(&Bs[c][tx * 4]);
-            const float av[4] = {a.x, a.y, a.z, a.w};
-            const float bv[4] = {bq.x, bq.y, bq.z, bq.w};
+            for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4*>(&As[(ty * 8 + i) * KG_PITCH + c]);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 8; ++j) {
+                const float4 bq = *reinterpret_cast<const float4*>(&Bs[(tx + 32 * j) * KG_PITCH + c]);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+                for (int i = 0; i < 8; ++i) {
+                    acc[i][j] = fmaf(a[i].x, bq.x, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].y, bq.y, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].z, bq.z, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].w, bq.w, acc[i][j]);
+                }
+            }
         }
         __syncthreads();
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int s = s0 + ty * 4 + i;
+    for (int i = 0; i < 8; ++i) {
+        const int s = s0 + ty * 8 + i;
         if (s >= S) continue;
-        const int self = seed_idx[ty * 4 + i];
-        float o[4];
+        const int self = seed_idx[ty * 8 + i];
+        float* row = D + ((size_t)b * S + s) * N;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int jj = j0 + tx * 4 + j;
-            o[j] = (jj == self) ? INFINITY : __fsub_rn(2.0f, __fmul_rn(2.0f, acc[i][j]));   // common.py:58-60
-        }
-        float* row = D + ((size_t)b * S + s) * N + j0 + tx * 4;
-        if (j0 + tx * 4 + 3 < N && (N & 3) == 0) {
-            *reinterpret_cast<float4*>(row) = make_float4(o[0], o[1], o[2], o[3]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (j0 + tx * 4 + j < N) row[j] = o[j];
+        for (int j = 0; j < 8; ++j) {
+            const int jj = j0 + tx + 32 * j;
+            if (jj < N) row[jj] = (jj == self) ? INFINITY : __fsub_rn(2.0f, __fmul_rn(2.0f, acc[i][j]));   // common.py:58-60
         }
     }
 }
