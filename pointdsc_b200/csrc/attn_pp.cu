@@ -850,8 +850,10 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.qk_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
     p.pv_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
     if (mode == PDSC_ATTN_SPLIT16) { const char* e = getenv("PDSC_ATTN_PV_TERMS"); if (e && atoi(e) >= 1 && atoi(e) <= 3) p.pv_terms = atoi(e); }
-    static int dbg = -1;                            // PDSC_ATTN_DBG: timing experiments only (results are wrong)
-    if (dbg < 0) { const char* e = getenv("PDSC_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
+    // PDSC_ATTN_DBG (read per call): selects the debug instantiation; bits 1 / 2 / 4 switch off the compat arithmetic,
+    // the exp, the MMAs (timing experiments only, results are then wrong); 8 sets no knob
+    const char* dbg_env = getenv("PDSC_ATTN_DBG");
+    const int dbg = dbg_env ? atoi(dbg_env) : 0;
     p.dbg = dbg;
     if (dbg & 4) p.qk_terms = p.pv_terms = 0;       // no MMAs
     const int smem_bytes = pp_smem_bytes();

@@ -294,6 +294,36 @@ def test_attention_split16_vs_oracle(N, grid, monkeypatch):
     assert err < 5e-5
 
 
+@pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation"])
+@pytest.mark.parametrize("grid", [None, "3"])
+@pytest.mark.parametrize("N", [100, 257, 700, 1300])
+def test_attention_launch_variants_vs_oracle(N, grid, variant, monkeypatch):
+    """The other instantiations of the attention kernel that live in the tree: the cluster-of-2 launch shape with TMA
+    multicast of the K / V tiles (PDSC_ATTN_CLUSTER=2; odd block counts leave one CTA of the last cluster on a phantom
+    block) and the debug instantiation (PDSC_ATTN_DBG=8: no knob set, same arithmetic)."""
+    from pointdsc_b200 import _cabi
+    if grid is None:
+        monkeypatch.delenv("PDSC_ATTN_GRID", raising=False)
+    else:
+        monkeypatch.setenv("PDSC_ATTN_GRID", grid)
+    if variant == "cluster2":
+        monkeypatch.setenv("PDSC_ATTN_CLUSTER", "2")
+    else:
+        monkeypatch.setenv("PDSC_ATTN_DBG", "8")
+    g = torch.Generator().manual_seed(3000 + N)
+    C, B = 128, 2
+    qkv = torch.randn(B, N, 3 * C, generator=g)
+    src = torch.rand(B, N, 3, generator=g)
+    tgt = src + 0.05 * torch.randn(B, N, 3, generator=g)
+    d = cu(qkv)
+    out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1, mode=_cabi.ATTN_SPLIT16)
+    torch.cuda.synchronize()
+    ref = _attn_ref(qkv, src, tgt, 0.1)
+    err = (out.cpu() - ref).abs().max().item()
+    print(f"split16 attention [{variant}] N={N} grid={grid}: max abs err {err:.3e}")
+    assert err < 5e-5
+
+
 def test_attention_split16_large_logits_trigger_rescale():
     """Row maxima that keep growing along the key axis exercise the lazy O rescale."""
     from pointdsc_b200 import _cabi
