@@ -51,6 +51,8 @@ extern "C" {
 #define PDSC_OP_SCORE_HYPOTHESES 5
 #define PDSC_OP_POST_REFINE 6
 #define PDSC_OP_POWER_ITER_FULL 7
+#define PDSC_OP_HYBRID_SEARCH 8      /* N = number of points */
+#define PDSC_OP_VOXEL_DOWN_SAMPLE 9  /* N = number of points, S = voxel-grid cells the workspace should hold */
 
 int pdsc_version(void);
 const char* pdsc_last_error(void);
@@ -210,6 +212,39 @@ int pdsc_registration_metrics(const float* trans, const float* gt_trans, const f
  *  counts int32 [P,4] = tp, fp, fn, tn; sums fp32 [P,2] = sum pred*gt, sum pred*(1-gt). */
 int pdsc_classification_counts(const float* pred, const float* gt, int P, int N, float thr,
                                int32_t* counts, float* sums, void* stream);
+
+/* ---- (N1) demo front end: what demo_registration.py:37-44,101-104 does through open3d 0.9 / numpy ----------------
+ * float64 throughout, as open3d and the demo's numpy lines are.  One cloud per call. */
+
+/* (N1) KDTreeSearchParamHybrid(radius, max_nn) for every point of the cloud against the cloud itself; replaces the
+ *  KDTreeFlann searches inside estimate_normals (utils/pointcloud.py:20-21) and compute_fpfh_feature
+ *  (demo_registration.py:41).  pts fp64 [n,3]; max_nn <= 128.  For query i: the up-to-max_nn points with
+ *  dist^2 < radius^2 (i itself included), ascending (dist^2, index): idx_out int32 [n,max_nn] (-1 padded),
+ *  dist2_out fp64 [n,max_nn] (+inf padded; nullable), count_out int32 [n] (nullable).
+ *  normals_out (nullable) fp64 [n,3]: open3d's EstimateNormals on those neighbours -- covariance from the running
+ *  sums, eigenvector of the smallest eigenvalue, not oriented; (0,0,1) with fewer than 3 neighbours.  With
+ *  idx_out == NULL only the normals are produced and no neighbour list is written. */
+int pdsc_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx_out, double* dist2_out,
+                       int32_t* count_out, double* normals_out, void* ws, size_t ws_bytes, void* stream);
+
+/* (N1) PointCloud.voxel_down_sample(voxel) (demo_registration.py:40): voxel index floor((p - (min - voxel/2)) / voxel),
+ *  mean point and normalised summed normal (nullable) per occupied voxel.  Output rows are the occupied voxels in
+ *  ascending (ix,iy,iz) (open3d's hash-map order is unspecified); out_pts / out_normals fp64 [n,3] capacity;
+ *  out_count int32 [1] (device) = number of rows, or -1 when the voxel grid has more cells than the workspace holds
+ *  (the int32 at byte 56 of ws then holds the number of cells needed: call again with
+ *  pdsc_workspace_bytes(PDSC_OP_VOXEL_DOWN_SAMPLE, 0, n, 0, cells, 0, 0)). */
+int pdsc_voxel_down_sample(const double* pts, const double* normals, int n, double voxel, double* out_pts,
+                           double* out_normals, int32_t* out_count, void* ws, size_t ws_bytes, void* stream);
+
+/* (N1) registration.compute_fpfh_feature (demo_registration.py:41) from the hybrid-search lists of the same cloud.
+ *  spfh_ws fp64 [n,33] scratch; fpfh_out fp64 [n,33] (row i = the 33 bins of point i). */
+int pdsc_fpfh(const double* pts, const double* normals, int n, const int32_t* idx, const double* dist2,
+              const int32_t* count, int max_nn, double* spfh_ws, double* fpfh_out, void* stream);
+
+/* (N1) argmin_j sqrt(2 - 2 a_i.b_j + 1e-6) in float64, first minimum (demo_registration.py:101-103).
+ *  A fp64 [Na,D], B fp64 [Nb,D], D <= 64; idx_out int64 [Na]; val_out (nullable) fp64 [Na] the minimum. */
+int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, int64_t* idx_out, double* val_out,
+                      void* stream);
 
 #ifdef __cplusplus
 }

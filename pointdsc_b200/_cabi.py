@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_float, c_int, c_int64, c_size_t, c_void_p
+from ctypes import c_double, c_float, c_int, c_int64, c_size_t, c_void_p
 
 import torch
 
@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
 ATTN_FP32, ATTN_SPLIT16, ATTN_FP16 = 0, 1, 2
 OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
 OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
+OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE = 8, 9
 
 # name -> (restype, argtypes); must list every symbol the header declares
 SIGNATURES = {
@@ -53,6 +54,12 @@ SIGNATURES = {
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                    c_void_p, c_void_p]),
     "pdsc_power_normalize": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_hybrid_search": (c_int, [c_void_p, c_int, c_double, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                   c_void_p]),
+    "pdsc_voxel_down_sample": (c_int, [c_void_p, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                       c_void_p]),
+    "pdsc_fpfh": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
                                      c_void_p, c_size_t, c_void_p]),
 }
@@ -427,3 +434,76 @@ def classification_counts(pred, gt, thr=0.0):
     _check(rc, "pdsc_classification_counts")
     _count()
     return counts, sums
+
+
+# ---- (N1) demo front end -------------------------------------------------------------------------
+def hybrid_search(pts, radius, max_nn, want_lists=True, want_normals=False, ws=None):
+    """pts fp64 [n,3] -> (idx int32 [n,max_nn], dist2 fp64 [n,max_nn], count int32 [n], normals fp64 [n,3] or None)
+    (pdsc_hybrid_search).  With want_lists=False only the normals are produced."""
+    lib = load()
+    n = pts.shape[0]
+    dev = pts.device
+    idx = torch.empty(n, max_nn, dtype=torch.int32, device=dev) if want_lists else None
+    d2 = torch.empty(n, max_nn, dtype=torch.float64, device=dev) if want_lists else None
+    cnt = torch.empty(n, dtype=torch.int32, device=dev)
+    nrm = torch.empty(n, 3, dtype=torch.float64, device=dev) if want_normals else None
+    buf = _ws(workspace_bytes(OP_HYBRID_SEARCH, N=n), dev, ws)
+    rc = lib.pdsc_hybrid_search(_ptr(pts, torch.float64, "pts"), n, float(radius), int(max_nn),
+                                idx.data_ptr() if want_lists else None, d2.data_ptr() if want_lists else None, cnt.data_ptr(),
+                                nrm.data_ptr() if want_normals else None, buf.data_ptr(), buf.numel(), _stream())
+    _check(rc, "pdsc_hybrid_search")
+    _count()
+    return idx, d2, cnt, nrm
+
+
+def voxel_down_sample(pts, normals, voxel, cells=1 << 22):
+    """pts fp64 [n,3], normals fp64 [n,3] or None -> (points [m,3], normals [m,3] or None), one row per occupied voxel
+    in ascending (ix,iy,iz) (pdsc_voxel_down_sample).  Reads the row count back (one host sync)."""
+    lib = load()
+    n = pts.shape[0]
+    dev = pts.device
+    out_p = torch.empty(n, 3, dtype=torch.float64, device=dev)
+    out_n = torch.empty(n, 3, dtype=torch.float64, device=dev) if normals is not None else None
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    for _ in range(2):
+        buf = torch.empty(workspace_bytes(OP_VOXEL_DOWN_SAMPLE, N=n, S=cells), dtype=torch.uint8, device=dev)
+        rc = lib.pdsc_voxel_down_sample(_ptr(pts, torch.float64, "pts"),
+                                        _ptr(normals, torch.float64, "normals") if normals is not None else None, n,
+                                        float(voxel), out_p.data_ptr(), out_n.data_ptr() if out_n is not None else None,
+                                        count.data_ptr(), buf.data_ptr(), buf.numel(), _stream())
+        _check(rc, "pdsc_voxel_down_sample")
+        _count()
+        m = int(count.item())
+        if m >= 0:
+            return out_p[:m], (out_n[:m] if out_n is not None else None)
+        cells = int(buf[56:60].view(torch.int32).item()) + 1024      # cells the grid needs (see the header)
+        if cells > (1 << 28):
+            break
+    raise RuntimeError("pdsc_voxel_down_sample: the voxel grid over the bounding box is too large for a dense grid")
+
+
+def fpfh(pts, normals, idx, d2, cnt):
+    """FPFH-33 fp64 [n,33] from the hybrid-search lists of the same cloud (pdsc_fpfh)."""
+    lib = load()
+    n, max_nn = idx.shape
+    spfh = torch.empty(n, 33, dtype=torch.float64, device=pts.device)
+    out = torch.empty(n, 33, dtype=torch.float64, device=pts.device)
+    rc = lib.pdsc_fpfh(_ptr(pts, torch.float64, "pts"), _ptr(normals, torch.float64, "normals"), n, _ptr(idx, torch.int32, "idx"),
+                       _ptr(d2, torch.float64, "dist2"), _ptr(cnt, torch.int32, "count"), max_nn, spfh.data_ptr(), out.data_ptr(),
+                       _stream())
+    _check(rc, "pdsc_fpfh")
+    _count()
+    return out
+
+
+def nn_match_f64(A, B, want_values=False):
+    """A fp64 [Na,D], B fp64 [Nb,D] -> idx int64 [Na] = argmin_j sqrt(2 - 2 a.b + 1e-6) (pdsc_nn_match_f64)."""
+    lib = load()
+    Na, D = A.shape
+    idx = torch.empty(Na, dtype=torch.int64, device=A.device)
+    val = torch.empty(Na, dtype=torch.float64, device=A.device) if want_values else None
+    rc = lib.pdsc_nn_match_f64(_ptr(A, torch.float64, "A"), _ptr(B, torch.float64, "B"), Na, B.shape[0], D, idx.data_ptr(),
+                               val.data_ptr() if want_values else None, _stream())
+    _check(rc, "pdsc_nn_match_f64")
+    _count()
+    return (idx, val) if want_values else idx

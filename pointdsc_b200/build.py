@@ -43,7 +43,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(job):
         src, obj = job
-        cmd = [NVCC] + ARCH_FLAGS + CFLAGS + ["-c", src, "-o", obj]
+        with open(src) as f:
+            first = f.readline()
+        extra = first.split("nvcc-flags:", 1)[1].split() if "nvcc-flags:" in first else []   # per-file flags (first line)
+        cmd = [NVCC] + ARCH_FLAGS + CFLAGS + extra + ["-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -77,6 +77,8 @@ size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode)
             return a > b ? a : b;
         }
         case PDSC_OP_PICK_SEEDS: return pick_seeds_workspace(B, N);
+        case PDSC_OP_HYBRID_SEARCH: return frontend_search_workspace(N);
+        case PDSC_OP_VOXEL_DOWN_SAMPLE: return frontend_voxel_workspace(N, S);
         case PDSC_OP_SEED_KNN: return seed_knn_workspace(B, N, S);
         case PDSC_OP_SEED_HYPOTHESES: return seed_hypotheses_workspace(B, S, k, 31);
         case PDSC_OP_SCORE_HYPOTHESES: return 0;
@@ -245,6 +247,38 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
     PDSC_REQUIRE(N > 0 && num_iterations > 0, "power_iter_full: bad arguments");
     return power_iter_full(src, tgt, v_out, N, sigma_spat, num_iterations, iters_out, ws, ws_bytes,
                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx_out, double* dist2_out,
+                       int32_t* count_out, double* normals_out, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(pts && ws && (idx_out || normals_out), "hybrid_search: null pointer");
+    PDSC_REQUIRE(n > 0 && max_nn > 0 && max_nn <= 128 && radius > 0.0, "hybrid_search: bad arguments n=%d max_nn=%d", n, max_nn);
+    PDSC_REQUIRE(!(dist2_out && !idx_out), "hybrid_search: dist2_out needs idx_out");
+    return launch_hybrid_search(pts, n, radius, max_nn, idx_out, dist2_out, count_out, normals_out, ws, ws_bytes,
+                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_voxel_down_sample(const double* pts, const double* normals, int n, double voxel, double* out_pts,
+                           double* out_normals, int32_t* out_count, void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(pts && out_pts && out_count && ws, "voxel_down_sample: null pointer");
+    PDSC_REQUIRE(!normals || out_normals, "voxel_down_sample: normals given but out_normals is null");
+    PDSC_REQUIRE(n > 0 && voxel > 0.0, "voxel_down_sample: bad arguments n=%d", n);
+    return launch_voxel_down_sample(pts, normals, n, voxel, out_pts, out_normals, out_count, ws, ws_bytes,
+                                    reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_fpfh(const double* pts, const double* normals, int n, const int32_t* idx, const double* dist2,
+              const int32_t* count, int max_nn, double* spfh_ws, double* fpfh_out, void* stream) {
+    PDSC_REQUIRE(pts && normals && idx && dist2 && count && spfh_ws && fpfh_out, "fpfh: null pointer");
+    PDSC_REQUIRE(n > 0 && max_nn > 0, "fpfh: bad arguments n=%d max_nn=%d", n, max_nn);
+    return launch_fpfh(pts, normals, n, idx, dist2, count, max_nn, spfh_ws, fpfh_out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, int64_t* idx_out, double* val_out,
+                      void* stream) {
+    PDSC_REQUIRE(A && B && idx_out, "nn_match_f64: null pointer");
+    PDSC_REQUIRE(Na > 0 && Nb > 0 && D > 0 && D <= 64, "nn_match_f64: bad shape Na=%d Nb=%d D=%d", Na, Nb, D);
+    return launch_nn_match_f64(A, B, Na, Nb, D, idx_out, val_out, reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

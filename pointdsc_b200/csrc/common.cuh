@@ -228,4 +228,14 @@ int power_iter_full(const float* src, const float* tgt, float* v_out, int N, flo
 int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,
                            size_t ws_bytes, cudaStream_t st);
 
+size_t frontend_search_workspace(int n);
+size_t frontend_voxel_workspace(int n, int max_cells);
+int launch_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx, double* d2, int32_t* cnt,
+                         double* normals, void* ws, size_t ws_bytes, cudaStream_t st);
+int launch_voxel_down_sample(const double* pts, const double* normals, int n, double voxel, double* out_pts,
+                             double* out_normals, int32_t* out_count, void* ws, size_t ws_bytes, cudaStream_t st);
+int launch_fpfh(const double* pts, const double* normals, int n, const int32_t* idx, const double* d2, const int32_t* cnt,
+                int max_nn, double* spfh, double* out, cudaStream_t st);
+int launch_nn_match_f64(const double* A, const double* Bm, int Na, int Nb, int D, int64_t* idx, double* val, cudaStream_t st);
+
 }  // namespace pdsc
