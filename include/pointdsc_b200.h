@@ -53,6 +53,7 @@ extern "C" {
 #define PDSC_OP_POWER_ITER_FULL 7
 #define PDSC_OP_HYBRID_SEARCH 8      /* N = number of points */
 #define PDSC_OP_VOXEL_DOWN_SAMPLE 9  /* N = number of points, S = voxel-grid cells the workspace should hold */
+#define PDSC_OP_NN_MATCH_F64 10      /* N = Na */
 
 int pdsc_version(void);
 const char* pdsc_last_error(void);
@@ -244,7 +245,7 @@ int pdsc_fpfh(const double* pts, const double* normals, int n, const int32_t* id
 /* (N1) argmin_j sqrt(2 - 2 a_i.b_j + 1e-6) in float64, first minimum (demo_registration.py:101-103).
  *  A fp64 [Na,D], B fp64 [Nb,D], D <= 64; idx_out int64 [Na]; val_out (nullable) fp64 [Na] the minimum. */
 int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, int64_t* idx_out, double* val_out,
-                      void* stream);
+                      void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus
 }

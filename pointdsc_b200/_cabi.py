@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
 ATTN_FP32, ATTN_SPLIT16, ATTN_FP16 = 0, 1, 2
 OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
 OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
-OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE = 8, 9
+OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE, OP_NN_MATCH_F64 = 8, 9, 10
 
 # name -> (restype, argtypes); must list every symbol the header declares
 SIGNATURES = {
@@ -59,7 +59,7 @@ SIGNATURES = {
     "pdsc_voxel_down_sample": (c_int, [c_void_p, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                        c_void_p]),
     "pdsc_fpfh": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
-    "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
                                      c_void_p, c_size_t, c_void_p]),
 }
@@ -496,14 +496,15 @@ def fpfh(pts, normals, idx, d2, cnt):
     return out
 
 
-def nn_match_f64(A, B, want_values=False):
+def nn_match_f64(A, B, want_values=False, ws=None):
     """A fp64 [Na,D], B fp64 [Nb,D] -> idx int64 [Na] = argmin_j sqrt(2 - 2 a.b + 1e-6) (pdsc_nn_match_f64)."""
     lib = load()
     Na, D = A.shape
     idx = torch.empty(Na, dtype=torch.int64, device=A.device)
     val = torch.empty(Na, dtype=torch.float64, device=A.device) if want_values else None
+    buf = _ws(workspace_bytes(OP_NN_MATCH_F64, N=Na), A.device, ws)
     rc = lib.pdsc_nn_match_f64(_ptr(A, torch.float64, "A"), _ptr(B, torch.float64, "B"), Na, B.shape[0], D, idx.data_ptr(),
-                               val.data_ptr() if want_values else None, _stream())
+                               val.data_ptr() if want_values else None, buf.data_ptr(), buf.numel(), _stream())
     _check(rc, "pdsc_nn_match_f64")
     _count()
     return (idx, val) if want_values else idx

@@ -79,6 +79,7 @@ size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode)
         case PDSC_OP_PICK_SEEDS: return pick_seeds_workspace(B, N);
         case PDSC_OP_HYBRID_SEARCH: return frontend_search_workspace(N);
         case PDSC_OP_VOXEL_DOWN_SAMPLE: return frontend_voxel_workspace(N, S);
+        case PDSC_OP_NN_MATCH_F64: return nn_match_f64_workspace(N);
         case PDSC_OP_SEED_KNN: return seed_knn_workspace(B, N, S);
         case PDSC_OP_SEED_HYPOTHESES: return seed_hypotheses_workspace(B, S, k, 31);
         case PDSC_OP_SCORE_HYPOTHESES: return 0;
@@ -275,10 +276,10 @@ int pdsc_fpfh(const double* pts, const double* normals, int n, const int32_t* id
 }
 
 int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, int64_t* idx_out, double* val_out,
-                      void* stream) {
-    PDSC_REQUIRE(A && B && idx_out, "nn_match_f64: null pointer");
+                      void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(A && B && idx_out && ws, "nn_match_f64: null pointer");
     PDSC_REQUIRE(Na > 0 && Nb > 0 && D > 0 && D <= 64, "nn_match_f64: bad shape Na=%d Nb=%d D=%d", Na, Nb, D);
-    return launch_nn_match_f64(A, B, Na, Nb, D, idx_out, val_out, reinterpret_cast<cudaStream_t>(stream));
+    return launch_nn_match_f64(A, B, Na, Nb, D, idx_out, val_out, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -60,7 +60,7 @@ __device__ __forceinline__ double blk_reduce(double v, bool is_min, double* sh) 
     return sh[0];
 }
 
-// mode 0: search grid (cell >= radius, x fastest, cell grows until the grid fits); mode 1: voxel grid
+// mode 0: search grid (x fastest, cell grows until the grid fits); mode 1: voxel grid
 // (origin = min - h/2 as open3d, z fastest so that the linear index ascends with (ix,iy,iz)).
 __global__ void __launch_bounds__(kScanThreads) grid_setup_kernel(const double* __restrict__ pts, int n, double h, int mode,
                                                                   int max_cells, GridParams* gp) {
@@ -294,39 +294,59 @@ __global__ void __launch_bounds__(kSearchThreads) hybrid_kernel(const double* __
         const int dx = gp->dims[0], dy = gp->dims[1], dz = gp->dims[2];
         const int cx = cell_coord(qx, gp->origin[0], gp->h, dx), cy = cell_coord(qy, gp->origin[1], gp->h, dy),
                   cz = cell_coord(qz, gp->origin[2], gp->h, dz);
-        const int x0 = max(cx - 1, 0), x1 = min(cx + 1, dx - 1);
         double wd = -1.0;    // current worst (largest) key in the list and its slot, valid once m == max_nn
         int wi = -1, wslot = 0;
-        for (int z = max(cz - 1, 0); z <= min(cz + 1, dz - 1); ++z)
-            for (int y = max(cy - 1, 0); y <= min(cy + 1, dy - 1); ++y) {
-                const int row = (z * dy + y) * dx;
-                const int b = start[row + x0], e = start[row + x1 + 1];
-                for (int c = b; c < e; ++c) {
-                    const double ex = sorted_xyz[(size_t)c * 3 + 0] - qx, ey = sorted_xyz[(size_t)c * 3 + 1] - qy,
-                                 ez = sorted_xyz[(size_t)c * 3 + 2] - qz;
-                    const double d2 = ex * ex + ey * ey + ez * ez;
-                    if (!(d2 < r2)) continue;
-                    if (m < max_nn) {
-                        const int id = sorted_idx[c];
-                        d2s[m * LD + t] = d2;
-                        ids[m * LD + t] = id;
-                        if (d2 > wd || (d2 == wd && id > wi)) { wd = d2; wi = id; wslot = m; }
-                        ++m;
-                    } else if (d2 <= wd) {
-                        const int id = sorted_idx[c];
-                        if (d2 < wd || id < wi) {
-                            d2s[wslot * LD + t] = d2;
-                            ids[wslot * LD + t] = id;
-                            wd = -1.0; wi = -1;
-                            for (int k = 0; k < max_nn; ++k) {
-                                const double dk = d2s[k * LD + t];
-                                const int ik = ids[k * LD + t];
-                                if (dk > wd || (dk == wd && ik > wi)) { wd = dk; wi = ik; wslot = k; }
-                            }
+        auto scan = [&](int b, int e) {
+            for (int c = b; c < e; ++c) {
+                const double ex = sorted_xyz[(size_t)c * 3 + 0] - qx, ey = sorted_xyz[(size_t)c * 3 + 1] - qy,
+                             ez = sorted_xyz[(size_t)c * 3 + 2] - qz;
+                const double d2 = ex * ex + ey * ey + ez * ez;
+                if (!(d2 < r2)) continue;
+                if (m < max_nn) {
+                    const int id = sorted_idx[c];
+                    d2s[m * LD + t] = d2;
+                    ids[m * LD + t] = id;
+                    if (d2 > wd || (d2 == wd && id > wi)) { wd = d2; wi = id; wslot = m; }
+                    ++m;
+                } else if (d2 <= wd) {
+                    const int id = sorted_idx[c];
+                    if (d2 < wd || id < wi) {
+                        d2s[wslot * LD + t] = d2;
+                        ids[wslot * LD + t] = id;
+                        wd = -1.0; wi = -1;
+                        for (int k = 0; k < max_nn; ++k) {
+                            const double dk = d2s[k * LD + t];
+                            const int ik = ids[k * LD + t];
+                            if (dk > wd || (dk == wd && ik > wi)) { wd = dk; wi = ik; wslot = k; }
                         }
                     }
                 }
             }
+        };
+        // Cells are visited in shells of growing Chebyshev distance rho around the query's cell.  Whatever lies outside
+        // shells 0..rho is farther than rho*h, so the walk ends as soon as the list is full and its worst entry is closer
+        // than that (or the shells cover the radius).
+        const double h = gp->h;
+        int last = (int)ceil(radius / h * (1.0 + 1e-9));
+        for (int rho = 0; rho <= last; ++rho) {
+            for (int oz = -rho; oz <= rho; ++oz) {
+                const int z = cz + oz;
+                if (z < 0 || z >= dz) continue;
+                for (int oy = -rho; oy <= rho; ++oy) {
+                    const int y = cy + oy;
+                    if (y < 0 || y >= dy) continue;
+                    const int row = (z * dy + y) * dx;
+                    if (max(abs(oz), abs(oy)) == rho) {
+                        scan(start[row + max(cx - rho, 0)], start[row + min(cx + rho, dx - 1) + 1]);
+                    } else {
+                        if (cx - rho >= 0) scan(start[row + cx - rho], start[row + cx - rho + 1]);
+                        if (cx + rho < dx) scan(start[row + cx + rho], start[row + cx + rho + 1]);
+                    }
+                }
+            }
+            const double safe = rho * h * (1.0 - 1e-9);
+            if (m == max_nn && wd < safe * safe) break;
+        }
         // ascending (d2, index): selection sort of the column
         for (int a = 0; a < m - 1; ++a) {
             int best = a;
@@ -509,41 +529,60 @@ __global__ void __launch_bounds__(128) fpfh_kernel(const double* __restrict__ sp
 }
 
 // ---- float64 descriptor matching -------------------------------------------------------------------------------------
-constexpr int kMatchThreads = 32;
-constexpr int kMatchTile = 64;
-constexpr int kMatchMaxD = 64;
+constexpr int kMatchThreads = 128;
+constexpr int kMatchTile = 32;
+constexpr int kMatchSplits = 8;
 
+// Thread = one A row held in registers; B rows broadcast from shared memory; the B range is cut into kMatchSplits
+// slices (blockIdx.y) whose (min, first argmin) are combined in slice order by match_reduce_kernel.
+template <int DMAX>
 __global__ void __launch_bounds__(kMatchThreads) nn_match_f64_kernel(const double* __restrict__ A, const double* __restrict__ Bm, int Na,
-                                                                     int Nb, int D, int64_t* __restrict__ idx_out,
-                                                                     double* __restrict__ val_out) {
+                                                                     int Nb, int D, double* __restrict__ part_val,
+                                                                     int64_t* __restrict__ part_idx) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* tile = reinterpret_cast<double*>(smem_raw);            // [kMatchTile][D]
-    double* arow = tile + (size_t)kMatchTile * D;                   // [D][kMatchThreads + 1]
     const int t = threadIdx.x;
     const int i = blockIdx.x * kMatchThreads + t;
-    for (int e = t; e < kMatchThreads * D; e += kMatchThreads) {
-        const int r = e / D, d = e % D;
-        const int src = blockIdx.x * kMatchThreads + r;
-        arow[d * (kMatchThreads + 1) + r] = (src < Na) ? A[(size_t)src * D + d] : 0.0;
-    }
+    double a[DMAX];
+#pragma unroll
+    for (int d = 0; d < DMAX; ++d) a[d] = (i < Na && d < D) ? A[(size_t)i * D + d] : 0.0;
+    const int chunk = (Nb + kMatchSplits - 1) / kMatchSplits;
+    const int jb = blockIdx.y * chunk, je = min(Nb, jb + chunk);
     double best = INFINITY;
     int64_t bi = 0;
-    for (int j0 = 0; j0 < Nb; j0 += kMatchTile) {
-        const int rows = min(kMatchTile, Nb - j0);
+    for (int j0 = jb; j0 < je; j0 += kMatchTile) {
+        const int rows = min(kMatchTile, je - j0);
         __syncthreads();
         for (int e = t; e < rows * D; e += kMatchThreads) tile[e] = Bm[(size_t)j0 * D + e];
         __syncthreads();
         for (int j = 0; j < rows; ++j) {
+            const double* b = tile + j * D;
             double acc = 0.0;
-            for (int d = 0; d < D; ++d) acc += arow[d * (kMatchThreads + 1) + t] * tile[j * D + d];
+#pragma unroll
+            for (int d = 0; d < DMAX; ++d)
+                if (d < D) acc += a[d] * b[d];
             const double dist = sqrt(2 - 2 * acc + 1e-6);
             if (dist < best) { best = dist; bi = j0 + j; }       // NaN never wins, first minimum kept (np.argmin)
         }
     }
     if (i < Na) {
-        idx_out[i] = bi;
-        if (val_out) val_out[i] = best;
+        part_val[(size_t)blockIdx.y * Na + i] = best;
+        part_idx[(size_t)blockIdx.y * Na + i] = bi;
     }
+}
+
+__global__ void match_reduce_kernel(const double* __restrict__ part_val, const int64_t* __restrict__ part_idx, int Na,
+                                    int64_t* __restrict__ idx_out, double* __restrict__ val_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Na) return;
+    double best = part_val[i];
+    int64_t bi = part_idx[i];
+    for (int s = 1; s < kMatchSplits; ++s) {
+        const double v = part_val[(size_t)s * Na + i];
+        if (v < best) { best = v; bi = part_idx[(size_t)s * Na + i]; }
+    }
+    idx_out[i] = bi;
+    if (val_out) val_out[i] = best;
 }
 
 struct GridWs {
@@ -584,6 +623,7 @@ int build_grid(const double* pts, int n, double h, int mode, int max_cells, cons
 }  // namespace
 
 constexpr int kSearchCells = 1 << 21;
+constexpr double kSearchShells = 4.0;   // search-grid cell = radius / 4 (grown if the grid would not fit)
 
 size_t frontend_search_workspace(int n) { return carve(nullptr, n, kSearchCells, true).bytes; }
 size_t frontend_voxel_workspace(int n, int max_cells) { return carve(nullptr, n, max_cells, false).bytes; }
@@ -595,7 +635,7 @@ int launch_hybrid_search(const double* pts, int n, double radius, int max_nn, in
         set_error("hybrid_search: workspace too small (%zu < %zu)", ws_bytes, g.bytes);
         return PDSC_ERR_WORKSPACE;
     }
-    int rc = build_grid(pts, n, radius, 0, kSearchCells, g, nullptr, st);
+    int rc = build_grid(pts, n, radius / kSearchShells, 0, kSearchCells, g, nullptr, st);
     if (rc) return rc;
     const size_t smem = (size_t)max_nn * (kSearchThreads + 1) * 12;
     const int blocks = (n + kSearchThreads - 1) / kSearchThreads;
@@ -639,11 +679,23 @@ int launch_fpfh(const double* pts, const double* normals, int n, const int32_t* 
     return check_launch("fpfh");
 }
 
-int launch_nn_match_f64(const double* A, const double* Bm, int Na, int Nb, int D, int64_t* idx, double* val, cudaStream_t st) {
-    const size_t smem = ((size_t)kMatchTile * D + (size_t)D * (kMatchThreads + 1)) * 8;
-    cudaFuncSetAttribute(nn_match_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    nn_match_f64_kernel<<<(Na + kMatchThreads - 1) / kMatchThreads, kMatchThreads, smem, st>>>(A, Bm, Na, Nb, D, idx, val);
-    count_launches(1);
+size_t nn_match_f64_workspace(int Na) { return (size_t)kMatchSplits * Na * 16 + 256; }
+
+int launch_nn_match_f64(const double* A, const double* Bm, int Na, int Nb, int D, int64_t* idx, double* val, void* ws,
+                        size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < nn_match_f64_workspace(Na)) {
+        set_error("nn_match_f64: workspace too small (%zu < %zu)", ws_bytes, nn_match_f64_workspace(Na));
+        return PDSC_ERR_WORKSPACE;
+    }
+    double* part_val = static_cast<double*>(ws);
+    int64_t* part_idx = reinterpret_cast<int64_t*>(part_val + (size_t)kMatchSplits * Na);
+    const size_t smem = (size_t)kMatchTile * D * 8;
+    dim3 grid((Na + kMatchThreads - 1) / kMatchThreads, kMatchSplits);
+    if (D <= 16) nn_match_f64_kernel<16><<<grid, kMatchThreads, smem, st>>>(A, Bm, Na, Nb, D, part_val, part_idx);
+    else if (D <= 33) nn_match_f64_kernel<33><<<grid, kMatchThreads, smem, st>>>(A, Bm, Na, Nb, D, part_val, part_idx);
+    else nn_match_f64_kernel<64><<<grid, kMatchThreads, smem, st>>>(A, Bm, Na, Nb, D, part_val, part_idx);
+    match_reduce_kernel<<<(Na + 255) / 256, 256, 0, st>>>(part_val, part_idx, Na, idx, val);
+    count_launches(2);
     return check_launch("nn_match_f64");
 }
 
