@@ -54,6 +54,7 @@ extern "C" {
 #define PDSC_OP_HYBRID_SEARCH 8      /* N = number of points */
 #define PDSC_OP_VOXEL_DOWN_SAMPLE 9  /* N = number of points, S = voxel-grid cells the workspace should hold */
 #define PDSC_OP_NN_MATCH_F64 10      /* N = Na */
+#define PDSC_OP_ICP_REFINE 11
 
 int pdsc_version(void);
 const char* pdsc_last_error(void);
@@ -246,6 +247,19 @@ int pdsc_fpfh(const double* pts, const double* normals, int n, const int32_t* id
  *  A fp64 [Na,D], B fp64 [Nb,D], D <= 64; idx_out int64 [Na]; val_out (nullable) fp64 [Na] the minimum. */
 int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, int64_t* idx_out, double* val_out,
                       void* ws, size_t ws_bytes, void* stream);
+
+/* (N4) point-to-point ICP on the key points; replaces icp_refine evaluation/benchmark_utils.py:40-56, i.e. open3d's
+ *  registration_icp(source, target, max_dist, init, TransformationEstimationPointToPoint()) with
+ *  ICPConvergenceCriteria(rel_fitness, rel_rmse, max_iter) (the reference uses 0.1 and the defaults 1e-6, 1e-6, 30).
+ *  src, tgt fp32 [B,N,3]; trans_inout fp32 [B,4,4] (initial transform in, refined out); B independent pairs.
+ *  Each round: every transformed source point is paired with its nearest target point closer than max_dist (ties to
+ *  the lower index), fitness = pairs / N, rmse over the pairs; stop when both change by less than the criteria,
+ *  else T <- Umeyama(pairs, no scaling) * T.  Arithmetic in float64.  Optional outputs: stats_out fp64 [B,2]
+ *  (fitness, inlier rmse of the last association), iters_out int32 [B] (updates applied), corr_out int32 [B,N]
+ *  (target index paired with each source point in the last association, -1 for none). */
+int pdsc_icp_refine(const float* src, const float* tgt, float* trans_inout, int B, int N, double max_dist, int max_iter,
+                    double rel_fitness, double rel_rmse, double* stats_out, int32_t* iters_out, int32_t* corr_out,
+                    void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
 ATTN_FP32, ATTN_SPLIT16, ATTN_FP16 = 0, 1, 2
 OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
 OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
-OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE, OP_NN_MATCH_F64 = 8, 9, 10
+OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE, OP_NN_MATCH_F64, OP_ICP_REFINE = 8, 9, 10, 11
 
 # name -> (restype, argtypes); must list every symbol the header declares
 SIGNATURES = {
@@ -60,6 +60,8 @@ SIGNATURES = {
                                        c_void_p]),
     "pdsc_fpfh": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_icp_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_double, c_int, c_double, c_double, c_void_p, c_void_p,
+                                c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
                                      c_void_p, c_size_t, c_void_p]),
 }
@@ -508,3 +510,23 @@ def nn_match_f64(A, B, want_values=False, ws=None):
     _check(rc, "pdsc_nn_match_f64")
     _count()
     return (idx, val) if want_values else idx
+
+
+# ---- (N4) ICP hand-off ---------------------------------------------------------------------------
+def icp_refine(src, tgt, trans, max_dist=0.1, max_iter=30, rel_fitness=1e-6, rel_rmse=1e-6, want_corr=False, ws=None):
+    """src, tgt fp32 [B,N,3], trans fp32 [B,4,4] -> (refined trans fp32 [B,4,4], stats fp64 [B,2] = fitness / inlier rmse,
+    iters int32 [B], corr int32 [B,N] or None) (pdsc_icp_refine)."""
+    lib = load()
+    B, N, _ = src.shape
+    dev = src.device
+    out = trans.detach().clone().contiguous()
+    stats = torch.empty(B, 2, dtype=torch.float64, device=dev)
+    iters = torch.empty(B, dtype=torch.int32, device=dev)
+    corr = torch.empty(B, N, dtype=torch.int32, device=dev) if want_corr else None
+    buf = _ws(workspace_bytes(OP_ICP_REFINE, B=B, N=N), dev, ws)
+    rc = lib.pdsc_icp_refine(_ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"), _ptr(out, torch.float32, "trans"), B, N,
+                             float(max_dist), int(max_iter), float(rel_fitness), float(rel_rmse), stats.data_ptr(), iters.data_ptr(),
+                             corr.data_ptr() if want_corr else None, buf.data_ptr(), buf.numel(), _stream())
+    _check(rc, "pdsc_icp_refine")
+    _count()
+    return out, stats, iters, corr

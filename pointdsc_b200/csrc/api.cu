@@ -80,6 +80,7 @@ size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode)
         case PDSC_OP_HYBRID_SEARCH: return frontend_search_workspace(N);
         case PDSC_OP_VOXEL_DOWN_SAMPLE: return frontend_voxel_workspace(N, S);
         case PDSC_OP_NN_MATCH_F64: return nn_match_f64_workspace(N);
+        case PDSC_OP_ICP_REFINE: return icp_workspace(B, N);
         case PDSC_OP_SEED_KNN: return seed_knn_workspace(B, N, S);
         case PDSC_OP_SEED_HYPOTHESES: return seed_hypotheses_workspace(B, S, k, 31);
         case PDSC_OP_SCORE_HYPOTHESES: return 0;
@@ -280,6 +281,15 @@ int pdsc_nn_match_f64(const double* A, const double* B, int Na, int Nb, int D, i
     PDSC_REQUIRE(A && B && idx_out && ws, "nn_match_f64: null pointer");
     PDSC_REQUIRE(Na > 0 && Nb > 0 && D > 0 && D <= 64, "nn_match_f64: bad shape Na=%d Nb=%d D=%d", Na, Nb, D);
     return launch_nn_match_f64(A, B, Na, Nb, D, idx_out, val_out, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_icp_refine(const float* src, const float* tgt, float* trans_inout, int B, int N, double max_dist, int max_iter,
+                    double rel_fitness, double rel_rmse, double* stats_out, int32_t* iters_out, int32_t* corr_out,
+                    void* ws, size_t ws_bytes, void* stream) {
+    PDSC_REQUIRE(src && tgt && trans_inout && ws, "icp_refine: null pointer");
+    PDSC_REQUIRE(B > 0 && N > 0 && max_dist > 0.0 && max_iter >= 0 && max_iter <= 1000, "icp_refine: bad arguments B=%d N=%d", B, N);
+    return launch_icp_refine(src, tgt, trans_inout, B, N, max_dist, max_iter, rel_fitness, rel_rmse, stats_out, iters_out,
+                             corr_out, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -236,6 +236,10 @@ int launch_voxel_down_sample(const double* pts, const double* normals, int n, do
                              double* out_normals, int32_t* out_count, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_fpfh(const double* pts, const double* normals, int n, const int32_t* idx, const double* d2, const int32_t* cnt,
                 int max_nn, double* spfh, double* out, cudaStream_t st);
+size_t icp_workspace(int B, int N);
+int launch_icp_refine(const float* src, const float* tgt, float* trans, int B, int N, double max_dist, int max_iter,
+                      double rel_fitness, double rel_rmse, double* stats, int32_t* iters, int32_t* corr, void* ws, size_t ws_bytes,
+                      cudaStream_t st);
 size_t nn_match_f64_workspace(int Na);
 int launch_nn_match_f64(const double* A, const double* Bm, int Na, int Nb, int D, int64_t* idx, double* val, void* ws,
                         size_t ws_bytes, cudaStream_t st);
