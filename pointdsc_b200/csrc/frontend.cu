@@ -15,6 +15,8 @@
 #include <float.h>
 #include <math.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace pdsc {
@@ -33,50 +35,52 @@ struct GridParams {
 };
 
 constexpr int kScanThreads = 1024;
-constexpr int kSearchThreads = 128;
 
 __device__ __forceinline__ int cell_coord(double p, double origin, double h, int dim) {
     int c = (int)floor((p - origin) / h);
     return min(max(c, 0), dim - 1);
 }
 
-__device__ __forceinline__ double blk_reduce(double v, bool is_min, double* sh) {
-    for (int o = 16; o > 0; o >>= 1) {
-        double w = __shfl_xor_sync(0xffffffffu, v, o);
-        v = is_min ? fmin(v, w) : fmax(v, w);
-    }
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        v = sh[threadIdx.x];
-        for (int o = 16; o > 0; o >>= 1) {
-            double w = __shfl_xor_sync(0xffffffffu, v, o);
-            v = is_min ? fmin(v, w) : fmax(v, w);
-        }
-        if (threadIdx.x == 0) sh[0] = v;
-    }
-    __syncthreads();
-    return sh[0];
+// Order-preserving map double -> uint64 (ascending doubles == ascending keys); keys of finite values are > 0.
+__device__ __forceinline__ unsigned long long dkey(double v) {
+    unsigned long long u = (unsigned long long)__double_as_longlong(v);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dkey_inv(unsigned long long k) {
+    unsigned long long u = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+    return __longlong_as_double((long long)u);
 }
 
-// mode 0: search grid (x fastest, cell grows until the grid fits); mode 1: voxel grid
-// (origin = min - h/2 as open3d, z fastest so that the linear index ascends with (ix,iy,iz)).
-__global__ void __launch_bounds__(kScanThreads) grid_setup_kernel(const double* __restrict__ pts, int n, double h, int mode,
-                                                                  int max_cells, GridParams* gp) {
-    __shared__ double sh[32];
+// bbox[0..2] = max over points of key(v), bbox[3..5] = max of ~key(v) (i.e. the minimum); zero-initialised by the memset.
+__global__ void __launch_bounds__(256) grid_bbox_kernel(const double* __restrict__ pts, int n, unsigned long long* __restrict__ bbox) {
     double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
-    for (int i = threadIdx.x; i < n; i += blockDim.x)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         for (int c = 0; c < 3; ++c) {
             double v = pts[(size_t)i * 3 + c];
             lo[c] = fmin(lo[c], v);
             hi[c] = fmax(hi[c], v);
         }
     for (int c = 0; c < 3; ++c) {
-        lo[c] = blk_reduce(lo[c], true, sh);
-        hi[c] = blk_reduce(hi[c], false, sh);
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[c] = fmin(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+            hi[c] = fmax(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+        }
+        if ((threadIdx.x & 31) == 0 && lo[c] <= hi[c]) {
+            atomicMax(&bbox[c], dkey(hi[c]));
+            atomicMax(&bbox[3 + c], ~dkey(lo[c]));
+        }
     }
-    if (threadIdx.x == 0) {
+}
+
+// mode 0: search grid (x fastest, cell grows until the grid fits); mode 1: voxel grid
+// (origin = min - h/2 as open3d, z fastest so that the linear index ascends with (ix,iy,iz)).
+__global__ void grid_setup_kernel(const unsigned long long* __restrict__ bbox, double h, int mode, int max_cells, GridParams* gp) {
+    double lo[3], hi[3];
+    for (int c = 0; c < 3; ++c) {
+        hi[c] = dkey_inv(bbox[c]);
+        lo[c] = dkey_inv(~bbox[3 + c]);
+    }
+    {
         GridParams g;
         g.status = 0;
         g.occupied = 0;
@@ -122,52 +126,111 @@ __global__ void grid_count_kernel(const double* __restrict__ pts, int n, const G
     atomicAdd(&count[c], 1);
 }
 
-// start[c] = exclusive prefix of count; rank[c] = exclusive prefix of (count > 0) (may be null); one CTA.
-__global__ void __launch_bounds__(kScanThreads) grid_scan_kernel(const int* __restrict__ count, int* __restrict__ start,
-                                                                 int* __restrict__ rank, GridParams* gp, int* occupied_out) {
-    __shared__ int sh_a[32], sh_b[32];
-    __shared__ int carry_a, carry_b;
+// Exclusive prefix sums over the cells, start[c] of count and rank[c] of (count > 0), in three steps: per-tile totals,
+// a one-CTA scan of the totals, per-tile scans with the tile's offset.
+constexpr int kTileCells = 4096;     // cells per scan tile (1024 threads x 4)
+
+__device__ __forceinline__ int2 block_exclusive_scan(int2 v, int2* total) {
+    __shared__ int2 warp_tot[32];
+    __shared__ int2 all;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int2 inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        int ta = __shfl_up_sync(0xffffffffu, inc.x, o), tb = __shfl_up_sync(0xffffffffu, inc.y, o);
+        if (lane >= o) { inc.x += ta; inc.y += tb; }
+    }
+    __syncthreads();
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int2 w = warp_tot[lane];
+        for (int o = 1; o < 32; o <<= 1) {
+            int ta = __shfl_up_sync(0xffffffffu, w.x, o), tb = __shfl_up_sync(0xffffffffu, w.y, o);
+            if (lane >= o) { w.x += ta; w.y += tb; }
+        }
+        warp_tot[lane] = w;
+        if (lane == 31) all = w;
+    }
+    __syncthreads();
+    int2 off = warp ? warp_tot[warp - 1] : make_int2(0, 0);
+    if (total) *total = all;
+    return make_int2(off.x + inc.x - v.x, off.y + inc.y - v.y);
+}
+
+__global__ void __launch_bounds__(kScanThreads) grid_tile_sum_kernel(const int* __restrict__ count, const GridParams* __restrict__ gp,
+                                                                     int2* __restrict__ tile_tot) {
+    if (gp->status) return;
+    const int ncells = gp->ncells;
+    const int base = blockIdx.x * kTileCells;
+    if (base >= ncells) return;
+    int2 v = make_int2(0, 0);
+    for (int k = 0; k < 4; ++k) {
+        const int c = base + k * kScanThreads + threadIdx.x;
+        const int a = c < ncells ? count[c] : 0;
+        v.x += a;
+        v.y += a > 0;
+    }
+    int2 tot;
+    block_exclusive_scan(v, &tot);
+    if (threadIdx.x == 0) tile_tot[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kScanThreads) grid_tile_scan_kernel(int2* __restrict__ tile_tot, int* __restrict__ start,
+                                                                      GridParams* gp, int* occupied_out) {
+    __shared__ int2 carry;
     if (gp->status) {
         if (threadIdx.x == 0 && occupied_out) *occupied_out = -1;
         return;
     }
     const int ncells = gp->ncells;
-    if (threadIdx.x == 0) { carry_a = 0; carry_b = 0; }
+    const int ntiles = (ncells + kTileCells - 1) / kTileCells;
+    if (threadIdx.x == 0) carry = make_int2(0, 0);
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < ncells; base += kScanThreads) {
-        int i = base + threadIdx.x;
-        int a = (i < ncells) ? count[i] : 0;
-        int b = a > 0 ? 1 : 0;
-        int sa = a, sb = b;
-        for (int o = 1; o < 32; o <<= 1) {
-            int ta = __shfl_up_sync(0xffffffffu, sa, o), tb = __shfl_up_sync(0xffffffffu, sb, o);
-            if (lane >= o) { sa += ta; sb += tb; }
-        }
-        if (lane == 31) { sh_a[warp] = sa; sh_b[warp] = sb; }
+    for (int base = 0; base < ntiles; base += kScanThreads) {
+        const int i = base + threadIdx.x;
+        int2 v = i < ntiles ? tile_tot[i] : make_int2(0, 0);
+        int2 tot;
+        int2 ex = block_exclusive_scan(v, &tot);
+        const int2 c = carry;
+        if (i < ntiles) tile_tot[i] = make_int2(c.x + ex.x, c.y + ex.y);
         __syncthreads();
-        if (warp == 0) {
-            int wa = sh_a[lane], wb = sh_b[lane];
-            for (int o = 1; o < 32; o <<= 1) {
-                int ta = __shfl_up_sync(0xffffffffu, wa, o), tb = __shfl_up_sync(0xffffffffu, wb, o);
-                if (lane >= o) { wa += ta; wb += tb; }
-            }
-            sh_a[lane] = wa; sh_b[lane] = wb;
-        }
-        __syncthreads();
-        int offa = carry_a + (warp ? sh_a[warp - 1] : 0), offb = carry_b + (warp ? sh_b[warp - 1] : 0);
-        if (i < ncells) {
-            start[i] = offa + sa - a;
-            if (rank) rank[i] = offb + sb - b;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) { carry_a += sh_a[31]; carry_b += sh_b[31]; }
+        if (threadIdx.x == 0) carry = make_int2(c.x + tot.x, c.y + tot.y);
         __syncthreads();
     }
     if (threadIdx.x == 0) {
-        start[ncells] = carry_a;
-        gp->occupied = carry_b;
-        if (occupied_out) *occupied_out = carry_b;
+        start[ncells] = carry.x;
+        gp->occupied = carry.y;
+        if (occupied_out) *occupied_out = carry.y;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) grid_tile_apply_kernel(const int* __restrict__ count, const int2* __restrict__ tile_off,
+                                                                       const GridParams* __restrict__ gp, int* __restrict__ start,
+                                                                       int* __restrict__ rank) {
+    if (gp->status) return;
+    const int ncells = gp->ncells;
+    const int base = blockIdx.x * kTileCells;
+    if (base >= ncells) return;
+    // thread t owns the 4 consecutive cells base + 4t .. base + 4t + 3
+    int a[4];
+    int2 v = make_int2(0, 0);
+    for (int k = 0; k < 4; ++k) {
+        const int c = base + threadIdx.x * 4 + k;
+        a[k] = c < ncells ? count[c] : 0;
+        v.x += a[k];
+        v.y += a[k] > 0;
+    }
+    int2 ex = block_exclusive_scan(v, nullptr);
+    const int2 off = tile_off[blockIdx.x];
+    int ra = off.x + ex.x, rb = off.y + ex.y;
+    for (int k = 0; k < 4; ++k) {
+        const int c = base + threadIdx.x * 4 + k;
+        if (c < ncells) {
+            start[c] = ra;
+            if (rank) rank[c] = rb;
+        }
+        ra += a[k];
+        rb += a[k] > 0;
     }
 }
 
@@ -269,8 +332,11 @@ __device__ V3 smallest_eigenvector(const double C[6]) {
 }
 
 // ---- hybrid search -------------------------------------------------------------------------------------------------
-// Shared memory: d2s[max_nn][T+1] doubles, ids[max_nn][T+1] ints (slot-major: a thread's list is a column).
-template <bool kNormals>
+// Shared memory: d2s[max_nn][T+1] doubles, ids[max_nn][T+1] ints, hist[kHistBins][T+1] ints (slot-major: a thread's list
+// and histogram are columns).
+constexpr int kHistBins = 48;
+
+template <bool kNormals, int kSearchThreads>
 __global__ void __launch_bounds__(kSearchThreads) hybrid_kernel(const double* __restrict__ pts, int n, const GridParams* __restrict__ gp,
                                                                 const int* __restrict__ start, const int* __restrict__ sorted_idx,
                                                                 const double* __restrict__ sorted_xyz, double radius, int max_nn,
@@ -280,6 +346,7 @@ __global__ void __launch_bounds__(kSearchThreads) hybrid_kernel(const double* __
     constexpr int LD = kSearchThreads + 1;
     double* d2s = reinterpret_cast<double*>(smem_raw);
     int* ids = reinterpret_cast<int*>(d2s + (size_t)max_nn * LD);
+    int* hist = ids + (size_t)max_nn * LD;              // [kHistBins][LD]
     __shared__ int sh_cnt[kSearchThreads];
     __shared__ int sh_row[kSearchThreads];
 
@@ -294,41 +361,11 @@ __global__ void __launch_bounds__(kSearchThreads) hybrid_kernel(const double* __
         const int dx = gp->dims[0], dy = gp->dims[1], dz = gp->dims[2];
         const int cx = cell_coord(qx, gp->origin[0], gp->h, dx), cy = cell_coord(qy, gp->origin[1], gp->h, dy),
                   cz = cell_coord(qz, gp->origin[2], gp->h, dz);
-        double wd = -1.0;    // current worst (largest) key in the list and its slot, valid once m == max_nn
-        int wi = -1, wslot = 0;
-        auto scan = [&](int b, int e) {
-            for (int c = b; c < e; ++c) {
-                const double ex = sorted_xyz[(size_t)c * 3 + 0] - qx, ey = sorted_xyz[(size_t)c * 3 + 1] - qy,
-                             ez = sorted_xyz[(size_t)c * 3 + 2] - qz;
-                const double d2 = ex * ex + ey * ey + ez * ez;
-                if (!(d2 < r2)) continue;
-                if (m < max_nn) {
-                    const int id = sorted_idx[c];
-                    d2s[m * LD + t] = d2;
-                    ids[m * LD + t] = id;
-                    if (d2 > wd || (d2 == wd && id > wi)) { wd = d2; wi = id; wslot = m; }
-                    ++m;
-                } else if (d2 <= wd) {
-                    const int id = sorted_idx[c];
-                    if (d2 < wd || id < wi) {
-                        d2s[wslot * LD + t] = d2;
-                        ids[wslot * LD + t] = id;
-                        wd = -1.0; wi = -1;
-                        for (int k = 0; k < max_nn; ++k) {
-                            const double dk = d2s[k * LD + t];
-                            const int ik = ids[k * LD + t];
-                            if (dk > wd || (dk == wd && ik > wi)) { wd = dk; wi = ik; wslot = k; }
-                        }
-                    }
-                }
-            }
-        };
-        // Cells are visited in shells of growing Chebyshev distance rho around the query's cell.  Whatever lies outside
-        // shells 0..rho is farther than rho*h, so the walk ends as soon as the list is full and its worst entry is closer
-        // than that (or the shells cover the radius).
+        // Cells are visited in shells of growing Chebyshev distance rho around the query's cell; whatever lies outside
+        // shells 0..rho is farther than rho*h.
         const double h = gp->h;
-        int last = (int)ceil(radius / h * (1.0 + 1e-9));
-        for (int rho = 0; rho <= last; ++rho) {
+        const int last = (int)ceil(radius / h * (1.0 + 1e-9));
+        auto walk_shell = [&](int rho, auto&& visit) {
             for (int oz = -rho; oz <= rho; ++oz) {
                 const int z = cz + oz;
                 if (z < 0 || z >= dz) continue;
@@ -337,16 +374,90 @@ __global__ void __launch_bounds__(kSearchThreads) hybrid_kernel(const double* __
                     if (y < 0 || y >= dy) continue;
                     const int row = (z * dy + y) * dx;
                     if (max(abs(oz), abs(oy)) == rho) {
-                        scan(start[row + max(cx - rho, 0)], start[row + min(cx + rho, dx - 1) + 1]);
+                        visit(start[row + max(cx - rho, 0)], start[row + min(cx + rho, dx - 1) + 1]);
                     } else {
-                        if (cx - rho >= 0) scan(start[row + cx - rho], start[row + cx - rho + 1]);
-                        if (cx + rho < dx) scan(start[row + cx + rho], start[row + cx + rho + 1]);
+                        if (cx - rho >= 0) visit(start[row + cx - rho], start[row + cx - rho + 1]);
+                        if (cx + rho < dx) visit(start[row + cx + rho], start[row + cx + rho + 1]);
                     }
                 }
             }
-            const double safe = rho * h * (1.0 - 1e-9);
-            if (m == max_nn && wd < safe * safe) break;
+        };
+        // Pass 1: histogram of dist^2 over logarithmic bins (exponent + 2 mantissa bits; the top bin ends at radius^2, the
+        // bottom one takes everything closer than radius/64).  The walk stops once the bin B* that holds the max_nn-th
+        // nearest candidate ends inside the region the visited shells cover.
+        const long long kmax = __double_as_longlong(r2) >> 50;
+        const long long kbase = kmax - (kHistBins - 1);
+        auto bin_of = [&](double d2) {
+            long long k = (__double_as_longlong(d2) >> 50) - kbase;
+            return (int)min(max(k, 0LL), (long long)(kHistBins - 1));
+        };
+        for (int c = 0; c < kHistBins; ++c) hist[c * LD + t] = 0;
+        int total = 0, bstar = kHistBins, rho_stop = last;
+        for (int rho = 0; rho <= last; ++rho) {
+            walk_shell(rho, [&](int b, int e) {
+                for (int c = b; c < e; ++c) {
+                    const double ex = sorted_xyz[(size_t)c * 3 + 0] - qx, ey = sorted_xyz[(size_t)c * 3 + 1] - qy,
+                                 ez = sorted_xyz[(size_t)c * 3 + 2] - qz;
+                    const double d2 = ex * ex + ey * ey + ez * ez;
+                    if (d2 < r2) { hist[bin_of(d2) * LD + t] += 1; ++total; }
+                }
+            });
+            if (total >= max_nn) {
+                int cum = 0, bb = 0;
+                for (; bb < kHistBins - 1; ++bb) {
+                    cum += hist[bb * LD + t];
+                    if (cum >= max_nn) break;
+                }
+                const double safe = rho * h * (1.0 - 1e-9);
+                const double edge = (bb >= kHistBins - 1) ? r2 : __longlong_as_double((kbase + bb + 1) << 50);
+                if (rho == last || edge <= safe * safe) { bstar = bb; rho_stop = rho; break; }
+            }
         }
+        // Pass 2: candidates in bins below B* are members for sure (fewer than max_nn of them); those in B* compete for the
+        // remaining slots (keep the smallest (dist^2, index), replacing the current worst).
+        int sure = 0;
+        for (int c = 0; c < min(bstar, kHistBins); ++c) sure += hist[c * LD + t];
+        const int room = max_nn - sure;      // slots [sure, max_nn) for the competitors; == max_nn - total (> 0) when bstar == kHistBins
+        int ns = 0, nc = 0;
+        double wd = -1.0;    // current worst (largest) key among the competitors and its slot, valid once nc == room
+        int wi = -1, wslot = 0;
+        for (int rho = 0; rho <= rho_stop; ++rho) {
+            walk_shell(rho, [&](int b, int e) {
+                for (int c = b; c < e; ++c) {
+                    const double ex = sorted_xyz[(size_t)c * 3 + 0] - qx, ey = sorted_xyz[(size_t)c * 3 + 1] - qy,
+                                 ez = sorted_xyz[(size_t)c * 3 + 2] - qz;
+                    const double d2 = ex * ex + ey * ey + ez * ez;
+                    if (!(d2 < r2)) continue;
+                    const int bin = bin_of(d2);
+                    if (bin < bstar) {
+                        d2s[ns * LD + t] = d2;
+                        ids[ns * LD + t] = sorted_idx[c];
+                        ++ns;
+                    } else if (bin == bstar) {
+                        if (nc < room) {
+                            const int id = sorted_idx[c];
+                            d2s[(sure + nc) * LD + t] = d2;
+                            ids[(sure + nc) * LD + t] = id;
+                            if (d2 > wd || (d2 == wd && id > wi)) { wd = d2; wi = id; wslot = sure + nc; }
+                            ++nc;
+                        } else if (d2 <= wd) {
+                            const int id = sorted_idx[c];
+                            if (d2 < wd || id < wi) {
+                                d2s[wslot * LD + t] = d2;
+                                ids[wslot * LD + t] = id;
+                                wd = -1.0; wi = -1;
+                                for (int k = sure; k < max_nn; ++k) {
+                                    const double dk = d2s[k * LD + t];
+                                    const int ik = ids[k * LD + t];
+                                    if (dk > wd || (dk == wd && ik > wi)) { wd = dk; wi = ik; wslot = k; }
+                                }
+                            }
+                        }
+                    }
+                }
+            });
+        }
+        m = sure + nc;
         // ascending (d2, index): selection sort of the column
         for (int a = 0; a < m - 1; ++a) {
             int best = a;
@@ -432,26 +543,28 @@ __global__ void voxel_reduce_kernel(const double* __restrict__ pts, const double
 }
 
 // ---- FPFH ----------------------------------------------------------------------------------------------------------
-constexpr int kSpfhThreads = 64;
-
 __device__ __forceinline__ int hist_bin(double x) {
     int h = (int)floor(x);
     return min(max(h, 0), 10);
 }
 
-__global__ void __launch_bounds__(kSpfhThreads) spfh_kernel(const double* __restrict__ pts, const double* __restrict__ nrm, int n,
-                                                            const int* __restrict__ idx, const int* __restrict__ cnt, int max_nn,
-                                                            double* __restrict__ spfh) {
-    __shared__ double hist[33][kSpfhThreads + 1];
-    const int t = threadIdx.x;
-    const int i = blockIdx.x * kSpfhThreads + t;
-    for (int b = 0; b < 33; ++b) hist[b][t] = 0.0;
-    if (i < n) {
-        const int m = cnt[i];
+// One warp per point, lanes over the neighbours.  Every neighbour adds the same increment to one bin of each group, so a
+// bin's value depends only on how many neighbours fell into it: the lanes count (shared-memory atomics), then each bin
+// repeats the sequential additions of the increment (what a scalar loop over the neighbours produces, bit for bit).
+__global__ void __launch_bounds__(128) spfh_kernel(const double* __restrict__ pts, const double* __restrict__ nrm, int n,
+                                                   const int* __restrict__ idx, const int* __restrict__ cnt, int max_nn,
+                                                   double* __restrict__ spfh) {
+    __shared__ int bins[4][33];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 4 + w;
+    bins[w][lane] = 0;
+    if (lane == 0) bins[w][32] = 0;
+    __syncwarp();
+    const int m = i < n ? cnt[i] : 0;
+    if (m > 1) {
         const V3 p1 = {pts[(size_t)i * 3], pts[(size_t)i * 3 + 1], pts[(size_t)i * 3 + 2]};
         const V3 n1 = {nrm[(size_t)i * 3], nrm[(size_t)i * 3 + 1], nrm[(size_t)i * 3 + 2]};
-        const double incr = 100.0 / (double)max(m - 1, 1);
-        for (int k = 1; k < m; ++k) {
+        for (int k = 1 + lane; k < m; k += 32) {
             const int j = idx[(size_t)i * max_nn + k];
             const V3 p2 = {pts[(size_t)j * 3], pts[(size_t)j * 3 + 1], pts[(size_t)j * 3 + 2]};
             const V3 n2 = {nrm[(size_t)j * 3], nrm[(size_t)j * 3 + 1], nrm[(size_t)j * 3 + 2]};
@@ -472,24 +585,26 @@ __global__ void __launch_bounds__(kSpfhThreads) spfh_kernel(const double* __rest
                 const double vn = sqrt(dot3(v, v));
                 if (vn != 0.0) {
                     v = {v.x / vn, v.y / vn, v.z / vn};
-                    const V3 w = cross3(n1c, v);
+                    const V3 ww = cross3(n1c, v);
                     f1 = dot3(v, n2c);
-                    f0 = atan2(dot3(w, n2c), dot3(n1c, n2c));
+                    f0 = atan2(dot3(ww, n2c), dot3(n1c, n2c));
                 } else {
                     f2 = 0.0;
                 }
             }
-            hist[hist_bin(11 * (f0 + M_PI) / (2.0 * M_PI))][t] += incr;
-            hist[11 + hist_bin(11 * (f1 + 1.0) * 0.5)][t] += incr;
-            hist[22 + hist_bin(11 * (f2 + 1.0) * 0.5)][t] += incr;
+            atomicAdd(&bins[w][hist_bin(11 * (f0 + M_PI) / (2.0 * M_PI))], 1);
+            atomicAdd(&bins[w][11 + hist_bin(11 * (f1 + 1.0) * 0.5)], 1);
+            atomicAdd(&bins[w][22 + hist_bin(11 * (f2 + 1.0) * 0.5)], 1);
         }
     }
-    __syncthreads();
-    // coalesced write-out of the CTA's rows
-    const int base = blockIdx.x * kSpfhThreads;
-    for (int e = t; e < kSpfhThreads * 33; e += kSpfhThreads) {
-        const int r = e / 33, b = e % 33;
-        if (base + r < n) spfh[(size_t)(base + r) * 33 + b] = hist[b][r];
+    __syncwarp();
+    if (i < n) {
+        const double incr = 100.0 / (double)max(m - 1, 1);
+        for (int b = lane; b < 33; b += 32) {
+            double v = 0.0;
+            for (int c = bins[w][b]; c > 0; --c) v += incr;
+            spfh[(size_t)i * 33 + b] = v;
+        }
     }
 }
 
@@ -504,12 +619,37 @@ __global__ void __launch_bounds__(128) fpfh_kernel(const double* __restrict__ sp
     const bool live = i < n;
     const int m = live ? cnt[i] : 0;
     double acc0 = 0.0, acc1 = 0.0;
-    for (int k = 1; k < m; ++k) {
-        const double dist = d2[(size_t)i * max_nn + k];
-        if (dist == 0.0) continue;
-        const int j = idx[(size_t)i * max_nn + k];
-        acc0 += spfh[(size_t)j * 33 + lane] / dist;
-        if (lane == 0) acc1 += spfh[(size_t)j * 33 + 32] / dist;
+    // lane l keeps list entries l, l+32, l+64, l+96 (max_nn <= 128); they are handed round by shuffles
+    int jj[4];
+    double dd[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const int k = c * 32 + lane;
+        jj[c] = (k < m) ? idx[(size_t)i * max_nn + k] : 0;
+        dd[c] = (k < m) ? d2[(size_t)i * max_nn + k] : 0.0;
+    }
+    for (int k0 = 0; k0 < m; k0 += 4) {
+        double r0[4], r1[4], dist[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k0 + u;
+            const int c = (k >> 5) & 3, srcl = k & 31;
+            int j = 0;
+            double dk = 0.0;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+                if (cc == c) { j = __shfl_sync(0xffffffffu, jj[cc], srcl); dk = __shfl_sync(0xffffffffu, dd[cc], srcl); }
+            const bool use = k >= 1 && k < m && dk != 0.0;
+            dist[u] = use ? dk : 0.0;
+            r0[u] = use ? spfh[(size_t)j * 33 + lane] : 0.0;
+            r1[u] = (use && lane == 0) ? spfh[(size_t)j * 33 + 32] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (dist[u] != 0.0) {            // ascending k: the order of a scalar loop
+                acc0 += r0[u] / dist[u];
+                if (lane == 0) acc1 += r1[u] / dist[u];
+            }
     }
     row[w][lane] = acc0;
     if (lane == 0) row[w][32] = acc1;
@@ -555,14 +695,33 @@ __global__ void __launch_bounds__(kMatchThreads) nn_match_f64_kernel(const doubl
         __syncthreads();
         for (int e = t; e < rows * D; e += kMatchThreads) tile[e] = Bm[(size_t)j0 * D + e];
         __syncthreads();
-        for (int j = 0; j < rows; ++j) {
+        int j = 0;
+        for (; j + 4 <= rows; j += 4) {
+            const double *b0 = tile + j * D, *b1 = b0 + D, *b2 = b1 + D, *b3 = b2 + D;
+            double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DMAX; ++d)
+                if (d < D) {
+                    acc0 += a[d] * b0[d];
+                    acc1 += a[d] * b1[d];
+                    acc2 += a[d] * b2[d];
+                    acc3 += a[d] * b3[d];
+                }
+            const double d0 = sqrt(2 - 2 * acc0 + 1e-6), d1 = sqrt(2 - 2 * acc1 + 1e-6), d2 = sqrt(2 - 2 * acc2 + 1e-6),
+                         d3 = sqrt(2 - 2 * acc3 + 1e-6);
+            if (d0 < best) { best = d0; bi = j0 + j; }           // NaN never wins, first minimum kept (np.argmin)
+            if (d1 < best) { best = d1; bi = j0 + j + 1; }
+            if (d2 < best) { best = d2; bi = j0 + j + 2; }
+            if (d3 < best) { best = d3; bi = j0 + j + 3; }
+        }
+        for (; j < rows; ++j) {
             const double* b = tile + j * D;
             double acc = 0.0;
 #pragma unroll
             for (int d = 0; d < DMAX; ++d)
                 if (d < D) acc += a[d] * b[d];
             const double dist = sqrt(2 - 2 * acc + 1e-6);
-            if (dist < best) { best = dist; bi = j0 + j; }       // NaN never wins, first minimum kept (np.argmin)
+            if (dist < best) { best = dist; bi = j0 + j; }
         }
     }
     if (i < Na) {
@@ -587,6 +746,8 @@ __global__ void match_reduce_kernel(const double* __restrict__ part_val, const i
 
 struct GridWs {
     GridParams* gp;
+    unsigned long long* bbox;
+    int2* tile_tot;
     int *count, *start, *rank, *fill, *cell_of, *sorted_idx;
     double* sorted_xyz;
     size_t bytes;
@@ -598,10 +759,12 @@ GridWs carve(void* ws, int n, int max_cells, bool want_xyz) {
     size_t off = 0;
     auto take = [&](size_t bytes) { void* r = p ? p + off : nullptr; off += align_up(bytes, 256); return r; };
     g.gp = static_cast<GridParams*>(take(sizeof(GridParams)));
+    g.bbox = static_cast<unsigned long long*>(take(6 * 8));          // bbox, count, fill: one memset
     g.count = static_cast<int*>(take((size_t)(max_cells + 1) * 4));
     g.fill = static_cast<int*>(take((size_t)(max_cells + 1) * 4));
     g.start = static_cast<int*>(take((size_t)(max_cells + 1) * 4));
     g.rank = static_cast<int*>(take((size_t)(max_cells + 1) * 4));
+    g.tile_tot = static_cast<int2*>(take(((size_t)max_cells / kTileCells + 2) * 8));
     g.cell_of = static_cast<int*>(take((size_t)n * 4));
     g.sorted_idx = static_cast<int*>(take((size_t)n * 4));
     g.sorted_xyz = want_xyz ? static_cast<double*>(take((size_t)n * 24)) : nullptr;
@@ -610,23 +773,26 @@ GridWs carve(void* ws, int n, int max_cells, bool want_xyz) {
 }
 
 int build_grid(const double* pts, int n, double h, int mode, int max_cells, const GridWs& g, int* occupied_out, cudaStream_t st) {
-    // count and fill are adjacent: one memset
-    cudaMemsetAsync(g.count, 0, (size_t)((unsigned char*)g.start - (unsigned char*)g.count), st);
-    grid_setup_kernel<<<1, kScanThreads, 0, st>>>(pts, n, h, mode, max_cells, g.gp);
+    cudaMemsetAsync(g.bbox, 0, (size_t)((unsigned char*)g.start - (unsigned char*)g.bbox), st);
+    const int ntiles = max_cells / kTileCells + 1;
+    grid_bbox_kernel<<<std::min((n + 255) / 256, 4 * num_sms()), 256, 0, st>>>(pts, n, g.bbox);
+    grid_setup_kernel<<<1, 1, 0, st>>>(g.bbox, h, mode, max_cells, g.gp);
     grid_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(pts, n, g.gp, g.cell_of, g.count);
-    grid_scan_kernel<<<1, kScanThreads, 0, st>>>(g.count, g.start, mode == 1 ? g.rank : nullptr, g.gp, occupied_out);
+    grid_tile_sum_kernel<<<ntiles, kScanThreads, 0, st>>>(g.count, g.gp, g.tile_tot);
+    grid_tile_scan_kernel<<<1, kScanThreads, 0, st>>>(g.tile_tot, g.start, g.gp, occupied_out);
+    grid_tile_apply_kernel<<<ntiles, kScanThreads, 0, st>>>(g.count, g.tile_tot, g.gp, g.start, mode == 1 ? g.rank : nullptr);
     grid_scatter_kernel<<<(n + 255) / 256, 256, 0, st>>>(pts, n, g.gp, g.cell_of, g.start, g.fill, g.sorted_idx, g.sorted_xyz);
-    count_launches(4);
+    count_launches(7);
     return check_launch("frontend grid");
 }
 
 }  // namespace
 
 constexpr int kSearchCells = 1 << 21;
-constexpr double kSearchShells = 4.0;   // search-grid cell = radius / 4 (grown if the grid would not fit)
+constexpr double kSearchShells = 4.0;   // search-grid cell = radius / 4 for large clouds (grown if the grid would not fit)
 
 size_t frontend_search_workspace(int n) { return carve(nullptr, n, kSearchCells, true).bytes; }
-size_t frontend_voxel_workspace(int n, int max_cells) { return carve(nullptr, n, max_cells, false).bytes; }
+size_t frontend_voxel_workspace(int n, int max_cells) { return carve(nullptr, n, 0, false).bytes + 17 * ((size_t)max_cells + 128); }
 
 int launch_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx, double* d2, int32_t* cnt,
                          double* normals, void* ws, size_t ws_bytes, cudaStream_t st) {
@@ -635,19 +801,25 @@ int launch_hybrid_search(const double* pts, int n, double radius, int max_nn, in
         set_error("hybrid_search: workspace too small (%zu < %zu)", ws_bytes, g.bytes);
         return PDSC_ERR_WORKSPACE;
     }
-    int rc = build_grid(pts, n, radius / kSearchShells, 0, kSearchCells, g, nullptr, st);
+    // dense scans fill the list long before the radius is reached: fine cells pay; small (down-sampled) clouds usually
+    // walk all the way out: fewer, larger cells
+    const double shells = n >= 65536 ? kSearchShells : 2.0;
+    int rc = build_grid(pts, n, radius / shells, 0, kSearchCells, g, nullptr, st);
     if (rc) return rc;
-    const size_t smem = (size_t)max_nn * (kSearchThreads + 1) * 12;
-    const int blocks = (n + kSearchThreads - 1) / kSearchThreads;
-    if (normals) {
-        cudaFuncSetAttribute(hybrid_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        hybrid_kernel<true><<<blocks, kSearchThreads, smem, st>>>(pts, n, g.gp, g.start, g.sorted_idx, g.sorted_xyz, radius, max_nn,
-                                                                  idx, d2, cnt, normals);
-    } else {
-        cudaFuncSetAttribute(hybrid_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        hybrid_kernel<false><<<blocks, kSearchThreads, smem, st>>>(pts, n, g.gp, g.start, g.sorted_idx, g.sorted_xyz, radius, max_nn,
-                                                                   idx, d2, cnt, nullptr);
-    }
+    // small clouds: 32-thread CTAs so that every SM gets work
+    const bool small = n < 128 * 2 * num_sms();
+    const int threads = small ? 32 : 128;
+    const size_t smem = (size_t)(max_nn * 12 + kHistBins * 4) * (threads + 1);
+    const int blocks = (n + threads - 1) / threads;
+#define PDSC_HYBRID(NRM, T)                                                                                                 \
+    do {                                                                                                                    \
+        cudaFuncSetAttribute(hybrid_kernel<NRM, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                \
+        hybrid_kernel<NRM, T><<<blocks, T, smem, st>>>(pts, n, g.gp, g.start, g.sorted_idx, g.sorted_xyz, radius, max_nn, idx, d2, \
+                                                        cnt, normals);                                                     \
+    } while (0)
+    if (normals) { if (small) PDSC_HYBRID(true, 32); else PDSC_HYBRID(true, 128); }
+    else { if (small) PDSC_HYBRID(false, 32); else PDSC_HYBRID(false, 128); }
+#undef PDSC_HYBRID
     count_launches(1);
     return check_launch("hybrid_search");
 }
@@ -656,14 +828,18 @@ int launch_voxel_down_sample(const double* pts, const double* normals, int n, do
                              int32_t* out_count, void* ws, size_t ws_bytes, cudaStream_t st) {
     // the grid takes whatever the workspace can hold
     const size_t fixed = carve(nullptr, n, 0, false).bytes;
-    if (ws_bytes < fixed + 4 * 4096) {
+    if (ws_bytes < fixed + 17 * 1024) {
         set_error("voxel_down_sample: workspace too small (%zu)", ws_bytes);
         return PDSC_ERR_WORKSPACE;
     }
-    long long mc = (long long)((ws_bytes - fixed) / 16) - 64;
+    long long mc = (long long)((ws_bytes - fixed) / 17) - 64;
     if (mc > 2000000000LL) mc = 2000000000LL;
     const int max_cells = (int)mc;
     GridWs g = carve(ws, n, max_cells, false);
+    if (g.bytes > ws_bytes) {
+        set_error("voxel_down_sample: workspace too small (%zu < %zu)", ws_bytes, g.bytes);
+        return PDSC_ERR_WORKSPACE;
+    }
     int rc = build_grid(pts, n, voxel, 1, max_cells, g, out_count, st);
     if (rc) return rc;
     voxel_reduce_kernel<<<(max_cells + 127) / 128, 128, 0, st>>>(pts, normals, g.gp, g.start, g.rank, g.sorted_idx, out_pts, out_normals);
@@ -673,7 +849,7 @@ int launch_voxel_down_sample(const double* pts, const double* normals, int n, do
 
 int launch_fpfh(const double* pts, const double* normals, int n, const int32_t* idx, const double* d2, const int32_t* cnt, int max_nn,
                 double* spfh, double* out, cudaStream_t st) {
-    spfh_kernel<<<(n + kSpfhThreads - 1) / kSpfhThreads, kSpfhThreads, 0, st>>>(pts, normals, n, idx, cnt, max_nn, spfh);
+    spfh_kernel<<<(n + 3) / 4, 128, 0, st>>>(pts, normals, n, idx, cnt, max_nn, spfh);
     fpfh_kernel<<<(n + 3) / 4, 128, 0, st>>>(spfh, n, idx, d2, cnt, max_nn, out);
     count_launches(2);
     return check_launch("fpfh");
