@@ -33,7 +33,8 @@ def load_golden(name):
     return meta, arrays
 
 
-GOLDEN_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("next_", "front_")))   # next_*: tests/test_next_oracle.py, front_*: tests/test_frontend_oracle.py
+GOLDEN_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("next_", "front_", "full_")))   # next_*: test_next_oracle.py, front_*: test_frontend_oracle.py, full_*: lean full-size fixtures
+FULL_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.startswith("full_") and f.endswith(".npz"))
 
 
 @pytest.fixture(scope="session")

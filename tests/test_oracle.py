@@ -47,6 +47,21 @@ def test_oracle_matches_reference_golden(case):
     assert len(out["refine_counts"]) in (len(ref_sizes) + 1, 20)
 
 
+def test_oracle_matches_reference_at_full_size():
+    """BASELINE configs[1] size (N=5000, 12 layers): the restatement against the unmodified reference's outputs."""
+    from conftest import load_golden as lg
+    meta, g = lg("full_3dmatch_n5000_l12")
+    p = synth.make_pair(meta["pair_seed"], meta["N"], **synth.CONFIGS[meta["family"]])
+    out = _run_oracle(meta, p)
+    assert (out["confidence"] - g["confidence"]).abs().max().item() <= 1e-5
+    assert torch.equal(out["seeds"].to(torch.int32), g["seeds"])
+    assert torch.equal(out["knn_idx"].to(torch.int32), g["knn_idx"])
+    assert torch.equal(out["inlier_count"], g["inlier_count"])
+    assert torch.equal(out["final_labels"].to(torch.uint8), g["final_labels"])
+    assert (out["final_trans"] - g["final_trans"]).abs().max().item() <= 1e-5
+    assert out["refine_counts"][:len(g["refine_sizes"])] == g["refine_sizes"].tolist()
+
+
 def test_power_iteration_known_answer():
     """Known-answer test in the spirit of misc/eigen.py:9-45: power iteration on random
     symmetric non-negative matrices converges to the eigh leading eigenvector."""
