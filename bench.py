@@ -46,12 +46,13 @@ def parse_args():
     ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "fp16"])
     ap.add_argument("--cpu-pairs", type=int, default=3, help="pairs in the cpu_baseline sample (first is warm-up)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--weight-seed", type=int, default=99, help="seed of the synthetic weights (oracle/synth.py)")
     return ap.parse_args()
 
 
 def workload_name(args):
     return f"synthetic {args.family}-shaped: {args.pairs} pairs x N={args.n} correspondences per GPU, " \
-           f"{NUM_LAYERS} layers, C={C}, seeded weights"
+           f"{NUM_LAYERS} layers, C={C}, seeded weights (seed {args.weight_seed})"
 
 
 def ncu_traffic(args):
@@ -86,6 +87,7 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
         self._halt = threading.Event()
+        self.recording = False
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -95,29 +97,37 @@ class ClockSampler(threading.Thread):
         except Exception:
             self.nv = None
 
+    _NAMES = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+              0x80: "hw_power_brake_slowdown"}
+
+    def _sample_once(self, keep):
+        nv = self.nv
+        try:
+            mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            try:
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            if keep:
+                self.samples.append(mhz)
+                for bit, name in self._NAMES.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+        except Exception:
+            pass
+
+    def prime(self):
+        """The first NVML queries of a process on a fresh box take tens of milliseconds and stall kernel launches while
+        they run: pay for them here, before the warm-up steps, not inside the timed region."""
+        if self.nv is not None:
+            for _ in range(3):
+                self._sample_once(False)
+
     def run(self):
         if self.nv is None:
             return
-        nv = self.nv
-        names = {
-            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake_slowdown",
-        }
         while not self._halt.is_set():
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                except Exception:
-                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if mask & bit:
-                        self.reasons.add(name)
-            except Exception:
-                pass
+            self._sample_once(self.recording)
             time.sleep(0.05)
 
     def stop(self):
@@ -134,8 +144,35 @@ def make_inputs(args, rank):
     base = 0 if args.family == "3dmatch" else 100
     seeds = [base + rank * args.pairs + i for i in range(args.pairs)]
     batch = synth.make_batch(seeds, args.n, **cfg)
-    sd = synth.make_state_dict(1234, num_layers=NUM_LAYERS, sigma_d=cfg["sigma_d"])
+    # weight seed 99: every confidence is positive at 12 layers, so the seed order is well defined and pair 0 of this batch
+    # is exactly the full-size golden case of tests/golden/full_*.npz (outputs of the unmodified reference); with seed 1234
+    # every confidence is negative and the reference fills the seed list from exact ties in argsort's unspecified order
+    sd = synth.make_state_dict(args.weight_seed, num_layers=NUM_LAYERS, sigma_d=cfg["sigma_d"])
     return cfg, batch, sd
+
+
+def golden_check(args, res):
+    """Pair 0 of the default workloads is the full-size golden case (tests/golden/full_*.npz: outputs of the unmodified
+    reference, oracle/gen_golden.py --full).  Compares the LAST timed step's result for that pair with it (outside the timed
+    region; reads a committed fixture, runs nothing from oracle/)."""
+    import json as _json
+    import numpy as np
+    name = {("3dmatch", 5000): "full_3dmatch_n5000_l12", ("kitti", 10000): "full_kitti_n10000_l12"}.get((args.family, args.n))
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", f"{name}.npz")
+    if name is None or not os.path.exists(path):
+        return None
+    z = np.load(path)
+    meta = _json.loads(bytes(z["meta"]).decode())
+    if meta["weight_seed"] != args.weight_seed or meta["num_layers"] != NUM_LAYERS:
+        return None
+    T = res["final_trans"][0].double().cpu()
+    G = torch.from_numpy(z["final_trans"])[0].double()
+    rot = float(torch.rad2deg(2 * torch.asin(torch.clamp(torch.linalg.matrix_norm(T[:3, :3] - G[:3, :3]) / (2 * 2 ** 0.5), max=1.0))))
+    return {"case": name, "against": "unmodified reference (committed golden vector), pair 0 of the timed batch",
+            "rot_err_deg": rot, "trans_err_m": float(torch.norm(T[:3, 3] - G[:3, 3])),
+            "max_abs_dconf": float((res["confidence"][0].cpu() - torch.from_numpy(z["confidence"])[0]).abs().max()),
+            "label_mismatches": int((res["final_labels"][0].cpu() != torch.from_numpy(z["final_labels"])[0].float()).sum()),
+            "tolerance": "rot <= 0.01 deg, trans <= 1e-4 m, conf <= 1e-4"}
 
 
 def cpu_baseline(args, cfg, batch, sd, n_pairs):
@@ -252,12 +289,21 @@ def main():
         flush.zero_()                       # L2 flush between steps (inside the timed region)
         return model(resident)
 
+    sampler = ClockSampler(local_rank)
+    sampler.prime()
+    sampler.start()                         # already polling during the warm-up; samples are kept from the timed region on
+    # Warm-up runs EXACTLY the code of the timed region (event-wrapped attention launches, step events, launch counter): on a
+    # fresh box the first execution of any host code path pages it in from the image, which costs milliseconds apiece.
+    setattr(_cabi, attn_name, timed_attn)   # CUDA events around the dominant kernel, same stream
+    w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0.record()
     for _ in range(args.warmup):
         step_resident()
+    w1.record()
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    setattr(_cabi, attn_name, timed_attn)   # CUDA events around the dominant kernel, same stream
+    _ = w0.elapsed_time(w1), [a.elapsed_time(b) for a, b in attn_events], _cabi.kernel_launches()
+    attn_events.clear()
+    sampler.recording = True
     launches0 = _cabi.kernel_launches()
     s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.perf_counter()
@@ -335,6 +381,9 @@ def main():
             "roofline": roofline,
             "wall_s_timed_region": t_wall,
         }
+        chk = golden_check(args, res)
+        if chk is not None:
+            line["parity_check"] = chk
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, cfg, batch, sd, args.cpu_pairs)
         _emit(line)
