@@ -171,6 +171,9 @@ def golden_check(args, res):
     return {"case": name, "against": "unmodified reference (committed golden vector), pair 0 of the timed batch",
             "rot_err_deg": rot, "trans_err_m": float(torch.norm(T[:3, 3] - G[:3, 3])),
             "max_abs_dconf": float((res["confidence"][0].cpu() - torch.from_numpy(z["confidence"])[0]).abs().max()),
+            "max_abs_dconf_vs_float64_reference": {
+                "ours": float((res["confidence"][0].cpu().double() - torch.from_numpy(z["confidence_f64"])[0]).abs().max()),
+                "fp32_reference": float((torch.from_numpy(z["confidence"])[0].double() - torch.from_numpy(z["confidence_f64"])[0]).abs().max())},
             "label_mismatches": int((res["final_labels"][0].cpu() != torch.from_numpy(z["final_labels"])[0].float()).sum()),
             "tolerance": "rot <= 0.01 deg, trans <= 1e-4 m, conf <= 1e-4"}
 

@@ -79,7 +79,16 @@ def main_full():
         model = ref_harness.build_reference_model(sd, **ctor)
         rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
         k = rec["knn_idx"].shape[-1]
+        # the same unmodified reference in float64: how far its own fp32 result is from exact arithmetic (the noise floor any
+        # fp32 implementation with another summation order lives on; 3.7e-5 in the confidences at KITTI scale)
+        torch.set_default_dtype(torch.float64)
+        try:
+            rec64 = ref_harness.run_reference(ref_harness.build_reference_model(sd, **ctor).double(), pair["corr_pos"].double(),
+                                              pair["src_keypts"].double(), pair["tgt_keypts"].double())
+        finally:
+            torch.set_default_dtype(torch.float32)
         arrays = {
+            "confidence_f64": rec64["confidence"], "final_trans_f64": rec64["final_trans"],
             "confidence": rec["confidence"], "seeds": rec["seeds"].to(torch.int32), "knn_idx": rec["knn_idx"].to(torch.int32),
             "seed_trans": rec["seed_trans"], "inlier_count": torch.round(rec["seed_fitness"] * FULL_CASES[name][1]).to(torch.int32),
             "initial_trans": rec["initial_trans"], "final_labels": rec["final_labels"].to(torch.uint8),

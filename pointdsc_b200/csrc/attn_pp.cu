@@ -301,12 +301,22 @@ __device__ __forceinline__ void pp_compat_pairs(const float4* pts, const float2 
 // key tiles of its block writes the message directly; otherwise the CTA stores its un-normalised
 // partial (O, m, l) and the LAST contributor of that block (atomic counter) combines them.
 // A CTA has at most two partial segments (its first and its last) -> two slots per CTA.
+// Chain limit: tcgen05 accumulates O in fp32 with truncation, so the error of one accumulation chain grows linearly with
+// the number of key tiles folded into the TMEM accumulator (measured on the N=10000 KITTI-shaped case: confidences drift
+// by 1.5e-4 when whole 157-tile blocks are accumulated in one go, 6e-5 with <= 48-tile chains).  For long blocks the
+// softmax threads therefore store O (and its reference max) every `chain` tiles of a segment into a slot of the workspace
+// (L2-resident, stores only) and the next PV MMA starts a fresh chain (accumulate = 0); the segment epilogue sums the
+// slots and the last chain with properly rounded fp32 adds.  No pipeline drain, no extra partials.  Production launch
+// shape only (the cluster-of-2 and debug instantiations run without the limit).
 // ------------------------------------------------------------------------------------------------
 struct PpParams {
     const uint8_t* Qw; const uint8_t* Kw; const uint8_t* Vw; const float* Pw;
     float* out; int64_t ld_out;
     float* part_o;          // [grid][2 slots][2 sub-tiles][128 rows][128 ch]
     float* part_ml;         // [grid][2][2][128][2]  (m, l)
+    float* chain_o;         // [grid][PP_CHAIN_SLOTS][2 sub-tiles][128 rows][128 ch]: O of the finished chains of the current segment
+    float* chain_m;         // [grid][PP_CHAIN_SLOTS][2][128]: the reference max each was stored with
+    int chain;              // key tiles per accumulation chain (0 = no limit)
     int* counters;          // [B * NRBp][2]
     int N, NT;              // rows, 64-key tiles per pair
     int NRBp;               // 256-row blocks per pair rounded up to even: tile / counter indexing
@@ -316,6 +326,7 @@ struct PpParams {
     long long* trace;       // optional timeline of CTA 0 (PDSC_ATTN_TRACE): trace[step * 16 + event] = SM clock
 };
 
+constexpr int PP_CHAIN_SLOTS = 8;     // finished chains per segment that the workspace holds
 struct PpSeg { int blk, j0, j1; };
 #define PP_TRACE(step, ev) do { if (tracing && (step) < 256) p.trace[(step) * 16 + (ev)] = clock64(); } while (0)
 
@@ -350,7 +361,7 @@ __device__ __forceinline__ float4 pp_ldcg4(const float* p) {
 // 256-row blocks; each loads HALF of every K / V^T tile and multicasts it to both (cp.async.bulk .multicast::cluster),
 // which halves the L2 -> SM traffic; a stage is released by both MMA issuers (multicast tcgen05.commit).
 // DBG: instantiation with the timing-experiment knobs (PDSC_ATTN_DBG) and the timeline trace compiled in.
-template <int CL, bool DBG>
+template <int CL, bool DBG, bool CHAIN = false>
 __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p) {
     constexpr int NP = 16;                   // key pairs per thread per tile (32 keys)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -461,11 +472,13 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 umma_commit_elect(&sm.s_full[1]);
                 if (CL == 1) umma_commit_elect(&sm.k_empty[kt & 1]); else umma_commit_elect_multicast(&sm.k_empty[kt & 1], CL_MASK);
             }
+            int next_chain = CHAIN ? p.chain : 0;     // first tile of the next accumulation chain
             for (int t = 0; t < n; ++t, ++kt) {
                 const int st = kt & 1, nx = st ^ 1;
                 const bool more = t + 1 < n;
                 const uint64_t vd = pp_uniform64(v_desc[st]), kd = pp_uniform64(k_desc[nx]);
-                const uint32_t acc = t > 0 ? 1u : 0u;
+                if (CHAIN && t == next_chain) next_chain += p.chain;
+                const uint32_t acc = (t == 0 || (CHAIN && t + p.chain == next_chain)) ? 0u : 1u;     // a fresh chain overwrites O
                 // ---- sub-tile A ----
                 mbar_wait_uniform(&sm.p_full[0], kt & 1);
                 PP_TRACE(kt, 2);
@@ -547,7 +560,10 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             }
             float m = 0.f, l = 0.f;                   // reference max (log2 units; compat = 0 keys sit at 0) and row sum
             const int n = s.j1 - s.j0;
-            for (int t = 0; t < n; ++t, ++kt) {
+            int t = 0, t_chain = 0;                   // t_chain: first tile of the current accumulation chain
+            do {
+            const int t_end = CHAIN ? min(n, t_chain + p.chain) : n;
+            for (; t < t_end; ++t, ++kt) {
                 const int st = kt & 1;
                 const int j = s.j0 + t;
                 // compatibilities of this thread's row against its 32 keys (needs only the points)
@@ -604,7 +620,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     const float2 ns = make_float2(-shift, -shift);
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = __fadd2_rn(e[i], ns);
-                    if (t > 0) {
+                    if (t > t_chain) {                 // (the first PV of a chain overwrites O: nothing to rescale yet)
                         mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);      // PV(t-1) has finished accumulating into O
                         tc_fence_after();
 #pragma unroll
@@ -656,10 +672,52 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 if (lane == 0) mbar_arrive(&sm.p_full[x]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 10 + x);
             }
+                if (CHAIN && t < n) {
+                    // Chain limit: the finished chain's O and its reference max go to this thread's slot of the workspace (stores
+                    // only: nothing waits for them); the first PV of the next chain overwrites O (accumulate = 0).
+                    mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);          // PV(t-1) has finished accumulating into O
+                    tc_fence_after();
+                    const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + (t / p.chain - 1)) * 2 + x) * PP_SUB + row;
+                    float* ca = p.chain_o + slot * PP_C + half * 64;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t r[32];
+                        tmem_ld_h32<64>(o_x + 32u * c, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4)
+                            __stcg(reinterpret_cast<uint4*>(ca + c * 32 + i), make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]));
+                    }
+                    if (half == 0) __stcg(p.chain_m + slot, m);
+                    t_chain = t;
+                }
+            } while (CHAIN && t < n);
             // ---- epilogue of the segment ----
             l += __shfl_xor_sync(0xffffffffu, l, 16);
             mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);
             tc_fence_after();
+            // O of the segment = the last chain (TMEM) + the finished chains (workspace slots, each relative to the reference
+            // max it was stored with)
+            const int nflush = CHAIN ? (n - 1) / p.chain : 0;
+            auto add_chains = [&](uint32_t (&r)[32], int c) {
+                if (CHAIN) {
+                    for (int k = 0; k < nflush; ++k) {
+                        const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + k) * 2 + x) * PP_SUB + row;
+                        const float4* ca = reinterpret_cast<const float4*>(p.chain_o + slot * PP_C + half * 64 + c * 32);
+                        float4 a[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) a[i] = __ldcg(ca + i);          // eight loads in flight
+                        const float f = exp2f(__ldcg(p.chain_m + slot) - m);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) + f * a[i].x);
+                            r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) + f * a[i].y);
+                            r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) + f * a[i].z);
+                            r[4 * i + 3] = __float_as_uint(__uint_as_float(r[4 * i + 3]) + f * a[i].w);
+                        }
+                    }
+                }
+            };
             if (s.j0 == 0 && s.j1 == NT) {
                 // all keys seen: msg = O / l, this thread writes 64 channels of its row
                 const float inv_l = 1.0f / l;
@@ -669,6 +727,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     uint32_t r[32];
                     tmem_ld_h32<64>(o_x + 32u * c, r);
                     tmem_ld_wait();
+                    add_chains(r, c);
                     if (grow < N) {
 #pragma unroll
                         for (int i = 0; i < 32; i += 4) {
@@ -690,6 +749,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     uint32_t r[32];
                     tmem_ld_h32<64>(o_x + 32u * c, r);
                     tmem_ld_wait();
+                    add_chains(r, c);
 #pragma unroll
                     for (int i = 0; i < 32; i += 4)
                         *reinterpret_cast<uint4*>(po + c * 32 + i) = make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
@@ -791,7 +851,7 @@ static int pp_grid(int B, int NU, int NT, int CL) {
 }
 
 struct PpLayout {
-    size_t q, k, v, pts, part_o, part_ml, counters, total;
+    size_t q, k, v, pts, part_o, part_ml, chain_o, chain_m, counters, total;
 };
 static PpLayout pp_layout(int B, int N) {
     const int NRB = (N + PP_BM - 1) / PP_BM, NT = (N + PP_BN - 1) / PP_BN;
@@ -807,6 +867,8 @@ static PpLayout pp_layout(int B, int N) {
     L.pts = off; off += align_up(t128 * 2 * PP_PTS_BYTES, 1024);
     L.part_o = off; off += G * 2 * 2 * PP_SUB * PP_C * sizeof(float);
     L.part_ml = off; off += G * 2 * 2 * PP_SUB * 2 * sizeof(float);
+    L.chain_o = off; off += (NT > 100 || getenv("PDSC_ATTN_CHAIN") ? (size_t)PP_CHAIN_SLOTS : 0) * G * 2 * PP_SUB * PP_C * sizeof(float);
+    L.chain_m = off; off += (size_t)PP_CHAIN_SLOTS * G * 2 * PP_SUB * sizeof(float);
     L.counters = off; off += align_up((size_t)B * NRBp * 2 * sizeof(int), 1024);
     L.total = off + 1024;
     return L;
@@ -839,6 +901,16 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.part_o = reinterpret_cast<float*>(base + L.part_o);
     p.part_ml = reinterpret_cast<float*>(base + L.part_ml);
     p.counters = reinterpret_cast<int*>(base + L.counters);
+    p.chain_o = reinterpret_cast<float*>(base + L.chain_o);
+    p.chain_m = reinterpret_cast<float*>(base + L.chain_m);
+    {   // chain limit (see the work-decomposition comment): on for blocks longer than 100 key tiles (N > 6400);
+        // PDSC_ATTN_CHAIN (read per call; a test/tuning knob) overrides the chain length, 0 = no limit.  At most
+        // PP_CHAIN_SLOTS finished chains per segment: very long blocks get proportionally longer chains.
+        const char* e = getenv("PDSC_ATTN_CHAIN");
+        p.chain = e ? atoi(e) : (NT > 100 ? 48 : 0);
+        if (p.chain < 0) p.chain = 0;
+        if (p.chain > 0 && (NT - 1) / p.chain > PP_CHAIN_SLOTS) p.chain = (NT - 1) / PP_CHAIN_SLOTS + 1;
+    }
     const int CL = pp_cluster();
     const int NRBp = (NRB + 1) & ~1;
     p.N = N; p.NT = NT; p.NRBp = NRBp;
@@ -862,6 +934,7 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
         cudaFuncSetAttribute(attn_pp_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         cudaFuncSetAttribute(attn_pp_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         cudaFuncSetAttribute(attn_pp_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaFuncSetAttribute(attn_pp_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         attr_set = true;
     }
     const int G = pp_grid(B, p.NU, NT, CL);
@@ -871,6 +944,8 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
     if (CL == 1 && (dbg || trace_path)) {
         attn_pp_kernel<1, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+    } else if (CL == 1 && p.chain > 0) {
+        attn_pp_kernel<1, false, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
     } else if (CL == 1) {
         attn_pp_kernel<1, false><<<G, PP_THREADS, smem_bytes, st>>>(p);
     } else {

@@ -294,22 +294,25 @@ def test_attention_split16_vs_oracle(N, grid, monkeypatch):
     assert err < 5e-5
 
 
-@pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation"])
+@pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation", "chain3", "chain1"])
 @pytest.mark.parametrize("grid", [None, "3"])
 @pytest.mark.parametrize("N", [100, 257, 700, 1300])
 def test_attention_launch_variants_vs_oracle(N, grid, variant, monkeypatch):
     """The other instantiations of the attention kernel that live in the tree: the cluster-of-2 launch shape with TMA
     multicast of the K / V tiles (PDSC_ATTN_CLUSTER=2; odd block counts leave one CTA of the last cluster on a phantom
-    block) and the debug instantiation (PDSC_ATTN_DBG=8: no knob set, same arithmetic)."""
+    block), the debug instantiation (PDSC_ATTN_DBG=8: no knob set, same arithmetic) and the chain limit that cuts every CTA
+    range into virtual ranges of at most PDSC_ATTN_CHAIN key tiles (on by default only for N > 6400)."""
     from pointdsc_b200 import _cabi
     if grid is None:
         monkeypatch.delenv("PDSC_ATTN_GRID", raising=False)
     else:
         monkeypatch.setenv("PDSC_ATTN_GRID", grid)
-    if variant == "cluster2":
+    if "cluster2" in variant:
         monkeypatch.setenv("PDSC_ATTN_CLUSTER", "2")
-    else:
+    if variant == "debug_instantiation":
         monkeypatch.setenv("PDSC_ATTN_DBG", "8")
+    if "chain" in variant:
+        monkeypatch.setenv("PDSC_ATTN_CHAIN", variant.split("chain")[1])
     g = torch.Generator().manual_seed(3000 + N)
     C, B = 128, 2
     qkv = torch.randn(B, N, 3 * C, generator=g)
