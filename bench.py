@@ -117,11 +117,15 @@ class ClockSampler(threading.Thread):
             pass
 
     def prime(self):
-        """The first NVML queries of a process on a fresh box take tens of milliseconds and stall kernel launches while
-        they run: pay for them here, before the warm-up steps, not inside the timed region."""
-        if self.nv is not None:
-            for _ in range(3):
-                self._sample_once(False)
+        """The first NVML queries of a process on a fresh box take tens of milliseconds each and stall kernel launches while
+        they run: keep querying here, before the warm-up steps, until they are fast (five in a row under 2 ms, 3 s at most)."""
+        if self.nv is None:
+            return
+        fast, t_end = 0, time.perf_counter() + 3.0
+        while fast < 5 and time.perf_counter() < t_end:
+            t0 = time.perf_counter()
+            self._sample_once(False)
+            fast = fast + 1 if time.perf_counter() - t0 < 2e-3 else 0
 
     def run(self):
         if self.nv is None:
@@ -305,6 +309,20 @@ def main():
     w1.record()
     barrier()
     _ = w0.elapsed_time(w1), [a.elapsed_time(b) for a, b in attn_events], _cabi.kernel_launches()
+    # settle: a fresh box keeps paying one-off costs (driver, clocks, page-ins) for a while after the first steps; extra
+    # untimed steps run until two consecutive ones agree within 3 % (at most 30), so the timed region starts in steady state
+    prev, settle_steps = None, 0
+    while settle_steps < 30:
+        w0.record()
+        step_resident()
+        w1.record()
+        torch.cuda.synchronize()
+        cur = w0.elapsed_time(w1)
+        settle_steps += 1
+        if prev is not None and abs(cur - prev) <= 0.03 * min(cur, prev):
+            break
+        prev = cur
+    barrier()
     attn_events.clear()
     sampler.recording = True
     launches0 = _cabi.kernel_launches()
@@ -376,6 +394,7 @@ def main():
             "config": {"workload": workload_name(args), "family": args.family, "pairs_per_step_per_gpu": args.pairs,
                        "N": args.n, "num_layers": NUM_LAYERS, "attn_mode": args.mode,
                        "l2": "256 MB buffer rewritten between steps (inside the timed region)",
+                       "extra_warmup_steps_until_steady": settle_steps,
                        "parallelism": f"pairs sharded over {world} GPU(s), no communication"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": e2e_ms / args.steps},
