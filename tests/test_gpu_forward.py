@@ -145,3 +145,45 @@ def test_full_size_properties(fam, N, mode):
     assert_trans_close(pres["final_trans"], res["final_trans"][0:1], rot=0.2, trans=0.25 * cfg["noise"])
     agree = (pres["final_labels"][0] == res["final_labels"][0, perm]).float().mean().item()
     assert agree > 0.99
+
+
+@pytest.mark.parametrize("N", [10, 17, 41, 100, 129])
+def test_forward_small_n_vs_oracle(N):
+    """Smallest inputs the reference itself can process (S = int(0.1 N) >= 1 seed; k = min(40, N-1) neighbours):
+    the whole forward against the CPU restatement."""
+    from pointdsc_b200 import PointDSC
+    cfg = synth.CONFIGS["3dmatch"]
+    L = 2
+    sd = synth.make_state_dict(99, num_layers=L, sigma_d=cfg["sigma_d"])
+    pair = synth.make_pair(500 + N, N, **dict(cfg, inlier_ratio=0.5))
+    model = PointDSC(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
+                     nms_radius=cfg["nms_radius"]).eval()
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda()
+    data = {k: pair[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    res = model(data)
+    ref = restate.forward_pair(sd, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"], num_layers=L,
+                               inlier_threshold=cfg["inlier_threshold"], nms_radius=cfg["nms_radius"])
+    assert res["final_trans"].shape == (1, 4, 4) and res["final_labels"].shape == (1, N)
+    assert res["seeds"].shape == ref["seeds"].shape
+    dconf = (res["confidence"].cpu() - ref["confidence"]).abs().max().item()
+    assert dconf <= CONF_TOL * max(1.0, ref["confidence"].abs().max().item())
+    if torch.equal(res["seeds"].cpu(), ref["seeds"]):
+        assert_trans_close(res["final_trans"], ref["final_trans"])
+        assert_labels_match(res["final_labels"][0], ref["final_labels"][0], res["initial_trans"][0], pair["src_keypts"][0],
+                            pair["tgt_keypts"][0], cfg["inlier_threshold"])
+    else:
+        print(f"[tie] N={N}: seed order differs (keys: {ref['seed_keys'][0, ref['seeds'][0]].tolist()[:6]} ...)")
+
+
+def test_forward_rejects_inputs_the_reference_cannot_process():
+    """N < 10 gives zero seeds: the reference fails inside cal_seed_trans (argmax of an empty tensor); the drop-in raises too."""
+    from pointdsc_b200 import PointDSC
+    cfg = synth.CONFIGS["3dmatch"]
+    model = PointDSC(num_layers=1).eval().cuda()
+    pair = synth.make_pair(1, 5, **cfg)
+    data = {k: pair[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    with pytest.raises((RuntimeError, ValueError, IndexError)):
+        model(data)
