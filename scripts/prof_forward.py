@@ -11,7 +11,7 @@ N = int(sys.argv[2]) if len(sys.argv) > 2 else 5000
 family = sys.argv[3] if len(sys.argv) > 3 else "3dmatch"
 cfg = synth.CONFIGS[family]
 batch = synth.make_batch(list(range(pairs)), N, **cfg)
-sd = synth.make_state_dict(1234, num_layers=12, sigma_d=cfg["sigma_d"])
+sd = synth.make_state_dict(99, num_layers=12, sigma_d=cfg["sigma_d"])
 model = PointDSC(num_layers=12, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"]).eval()
 model.load_state_dict(sd, strict=True)
 model = model.cuda()
