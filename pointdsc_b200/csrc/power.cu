@@ -4,28 +4,42 @@
 // The matrix (10 GB at N=50k) is never stored: each M.v recomputes it from 6 floats per
 // correspondence.  Rows are independent, so a rank can own a row range (row sharding) and
 // all-gather y; the normalisation + allclose test is a one-block kernel every rank repeats.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace pdsc {
 
 constexpr int MV_ROWS = 64, MV_SLICES = 4, MV_THREADS = MV_ROWS * MV_SLICES, MV_TILE = 512;
+constexpr int MV_KS = 8;        // column splits = CTAs per cluster
 
-__global__ void __launch_bounds__(MV_THREADS) compat_matvec_kernel(const float* __restrict__ src,
-                                                                   const float* __restrict__ tgt,
-                                                                   const float* __restrict__ v, float* __restrict__ y,
-                                                                   int N, int row_begin, int row_end, float sig2,
-                                                                   const int32_t* __restrict__ converged_flag) {
-    if (converged_flag && *converged_flag) return;
+// y[r] = sum_j M[r,j] v[j] for 64 rows per CLUSTER of 8 CTAs: CTA k of the cluster takes the k-th eighth of the column
+// tiles, the eight partial sums meet in distributed shared memory and rank 0 adds them in a fixed order.  The split does
+// not depend on the row range, so a row-sharded run (any number of ranks) produces the same bits as a single GPU, and a
+// rank that owns only N/8 rows still fills the machine (98 row blocks x 8 = 784 CTAs at N = 50000 on 8 GPUs).
+__global__ void __cluster_dims__(1, MV_KS, 1) __launch_bounds__(MV_THREADS)
+compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tgt, const float* __restrict__ v,
+                     float* __restrict__ y, int N, int row_begin, int row_end, float sig2,
+                     const int32_t* __restrict__ converged_flag) {
+    if (converged_flag && *converged_flag) return;          // uniform over the grid
+    cg::cluster_group cluster = cg::this_cluster();
     __shared__ float4 ta[MV_TILE];   // src xyz, v
     __shared__ float4 tb[MV_TILE];   // tgt xyz, unused
     __shared__ float part[MV_SLICES][MV_ROWS];
+    __shared__ float csum[MV_ROWS];  // this CTA's partial sums, read by rank 0 of the cluster
     const int rl = threadIdx.x % MV_ROWS, slice = threadIdx.x / MV_ROWS;
+    const int ks = blockIdx.y;                                // == rank in the cluster
     const int r = row_begin + blockIdx.x * MV_ROWS + rl;
     const int rc = min(r, N - 1);
     const float sx = src[rc * 3], sy = src[rc * 3 + 1], sz = src[rc * 3 + 2];
     const float tx = tgt[rc * 3], ty = tgt[rc * 3 + 1], tz = tgt[rc * 3 + 2];
+    const int ntiles = (N + MV_TILE - 1) / MV_TILE;
+    const int t_lo = (int)((long long)ntiles * ks / MV_KS), t_hi = (int)((long long)ntiles * (ks + 1) / MV_KS);
     float acc = 0.f;
-    for (int j0 = 0; j0 < N; j0 += MV_TILE) {
+    for (int tile = t_lo; tile < t_hi; ++tile) {
+        const int j0 = tile * MV_TILE;
         const int nj = min(MV_TILE, N - j0);
         __syncthreads();
         for (int t = threadIdx.x; t < nj; t += MV_THREADS) {
@@ -45,7 +59,15 @@ __global__ void __launch_bounds__(MV_THREADS) compat_matvec_kernel(const float* 
     }
     part[slice][rl] = acc;
     __syncthreads();
-    if (slice == 0 && r < row_end) y[r - row_begin] = (part[0][rl] + part[1][rl]) + (part[2][rl] + part[3][rl]);
+    if (slice == 0) csum[rl] = (part[0][rl] + part[1][rl]) + (part[2][rl] + part[3][rl]);
+    cluster.sync();
+    if (ks == 0 && slice == 0 && r < row_end) {
+        float c[MV_KS];
+#pragma unroll
+        for (int k = 0; k < MV_KS; ++k) c[k] = cluster.map_shared_rank(csum, k)[rl];
+        y[r - row_begin] = ((c[0] + c[1]) + (c[2] + c[3])) + ((c[4] + c[5]) + (c[6] + c[7]));
+    }
+    cluster.sync();                                           // peers keep their shared memory until rank 0 has read it
 }
 
 __global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __restrict__ y, float* __restrict__ v,
@@ -91,7 +113,7 @@ int launch_compat_matvec(const float* src, const float* tgt, const float* v, flo
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st) {
     const int rows = row_end - row_begin;
     if (rows <= 0) return PDSC_OK;
-    compat_matvec_kernel<<<(rows + MV_ROWS - 1) / MV_ROWS, MV_THREADS, 0, st>>>(
+    compat_matvec_kernel<<<dim3((rows + MV_ROWS - 1) / MV_ROWS, MV_KS), MV_THREADS, 0, st>>>(
         src, tgt, v, y, N, row_begin, row_end, sigma_spat * sigma_spat, converged_flag);
     count_launches(1);
     return check_launch("compat_matvec");

@@ -54,8 +54,11 @@ def power_iteration_full_sharded(src, tgt, sigma_spat, num_iterations, group=Non
         matvec(src, tgt, v, r0, r1, sigma_spat, converged_flag=flag, out=y_loc[: r1 - r0])
         if world > 1:
             dist.all_gather_into_tensor(y_full, y_loc, group=group)
-            for r, (a, b) in enumerate(bounds):
-                y[a:b] = y_full[r * width: r * width + (b - a)]
+            if world * width == N:                      # equal shards: the gathered buffer is y
+                y = y_full
+            else:
+                for r, (a, b) in enumerate(bounds):
+                    y[a:b] = y_full[r * width: r * width + (b - a)]
         else:
             y[:] = y_loc[:N]
         normalize(y, v, flag, iters)
