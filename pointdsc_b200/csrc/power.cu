@@ -7,65 +7,97 @@
 #include <cooperative_groups.h>
 
 #include "common.cuh"
+#include "sm100.cuh"
 
 namespace cg = cooperative_groups;
 
 namespace pdsc {
 
-constexpr int MV_ROWS = 64, MV_SLICES = 4, MV_THREADS = MV_ROWS * MV_SLICES, MV_TILE = 512;
+constexpr int MV_LANES = 64, MV_RPT = 2, MV_ROWS = MV_LANES * MV_RPT, MV_SLICES = 4, MV_THREADS = MV_LANES * MV_SLICES,
+              MV_TILE = 512;
 constexpr int MV_KS = 8;        // column splits = CTAs per cluster
 
-// y[r] = sum_j M[r,j] v[j] for 64 rows per CLUSTER of 8 CTAs: CTA k of the cluster takes the k-th eighth of the column
-// tiles, the eight partial sums meet in distributed shared memory and rank 0 adds them in a fixed order.  The split does
-// not depend on the row range, so a row-sharded run (any number of ranks) produces the same bits as a single GPU, and a
-// rank that owns only N/8 rows still fills the machine (98 row blocks x 8 = 784 CTAs at N = 50000 on 8 GPUs).
+__device__ __forceinline__ float mv_fma_sat(float a, float b, float c) {
+    float d;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// y[r] = sum_j M[r,j] v[j], M[r,j] = max(0, 1 - (|s_r - s_j| - |t_r - t_j|)^2 / sigma^2), M[r,r] = 0, for 128 rows per
+// CLUSTER of 8 CTAs: CTA k of the cluster takes the k-th eighth of the column tiles, the eight partial sums meet in
+// distributed shared memory and rank 0 adds them in a fixed order.  The split does not depend on the row range, so a
+// row-sharded run (any number of ranks) produces the same bits as a single GPU, and a rank that owns only N/8 rows still
+// fills the machine.  Arithmetic: points are scaled by 1/sigma when a tile is staged (no division per entry), a thread
+// owns two rows as the two lanes of packed f32x2 adds / FMAs, distances by sqrt.approx (MUFU), 1 - c^2 by one saturating
+// FMA: 2 MUFU + ~9 packed FP32 instructions per pair of entries (the exact-rounding form it replaces cost ~50 per entry).
 __global__ void __cluster_dims__(1, MV_KS, 1) __launch_bounds__(MV_THREADS)
 compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tgt, const float* __restrict__ v,
-                     float* __restrict__ y, int N, int row_begin, int row_end, float sig2,
+                     float* __restrict__ y, int N, int row_begin, int row_end, float inv_sigma,
                      const int32_t* __restrict__ converged_flag) {
     if (converged_flag && *converged_flag) return;          // uniform over the grid
     cg::cluster_group cluster = cg::this_cluster();
-    __shared__ float4 ta[MV_TILE];   // src xyz, v
-    __shared__ float4 tb[MV_TILE];   // tgt xyz, unused
-    __shared__ float part[MV_SLICES][MV_ROWS];
-    __shared__ float csum[MV_ROWS];  // this CTA's partial sums, read by rank 0 of the cluster
-    const int rl = threadIdx.x % MV_ROWS, slice = threadIdx.x / MV_ROWS;
+    __shared__ float4 ta[MV_TILE];   // src xyz / sigma, v
+    __shared__ float4 tb[MV_TILE];   // tgt xyz / sigma, unused
+    __shared__ float2 part[MV_SLICES][MV_LANES];
+    __shared__ float2 csum[MV_LANES];  // this CTA's partial sums (rows rl and rl + 64), read by rank 0 of the cluster
+    const int rl = threadIdx.x % MV_LANES, slice = threadIdx.x / MV_LANES;
     const int ks = blockIdx.y;                                // == rank in the cluster
-    const int r = row_begin + blockIdx.x * MV_ROWS + rl;
-    const int rc = min(r, N - 1);
-    const float sx = src[rc * 3], sy = src[rc * 3 + 1], sz = src[rc * 3 + 2];
-    const float tx = tgt[rc * 3], ty = tgt[rc * 3 + 1], tz = tgt[rc * 3 + 2];
+    const int r0 = row_begin + blockIdx.x * MV_ROWS + rl, r1 = r0 + MV_LANES;
+    const int c0 = min(r0, N - 1), c1 = min(r1, N - 1);
+    const float2 sx = make_float2(src[c0 * 3] * inv_sigma, src[c1 * 3] * inv_sigma),
+                 sy = make_float2(src[c0 * 3 + 1] * inv_sigma, src[c1 * 3 + 1] * inv_sigma),
+                 sz = make_float2(src[c0 * 3 + 2] * inv_sigma, src[c1 * 3 + 2] * inv_sigma);
+    const float2 tx = make_float2(tgt[c0 * 3] * inv_sigma, tgt[c1 * 3] * inv_sigma),
+                 ty = make_float2(tgt[c0 * 3 + 1] * inv_sigma, tgt[c1 * 3 + 1] * inv_sigma),
+                 tz = make_float2(tgt[c0 * 3 + 2] * inv_sigma, tgt[c1 * 3 + 2] * inv_sigma);
     const int ntiles = (N + MV_TILE - 1) / MV_TILE;
     const int t_lo = (int)((long long)ntiles * ks / MV_KS), t_hi = (int)((long long)ntiles * (ks + 1) / MV_KS);
-    float acc = 0.f;
+    float2 acc = make_float2(0.f, 0.f);
     for (int tile = t_lo; tile < t_hi; ++tile) {
         const int j0 = tile * MV_TILE;
         const int nj = min(MV_TILE, N - j0);
         __syncthreads();
         for (int t = threadIdx.x; t < nj; t += MV_THREADS) {
             const int j = j0 + t;
-            ta[t] = make_float4(src[j * 3], src[j * 3 + 1], src[j * 3 + 2], v[j]);
-            tb[t] = make_float4(tgt[j * 3], tgt[j * 3 + 1], tgt[j * 3 + 2], 0.f);
+            ta[t] = make_float4(src[j * 3] * inv_sigma, src[j * 3 + 1] * inv_sigma, src[j * 3 + 2] * inv_sigma, v[j]);
+            tb[t] = make_float4(tgt[j * 3] * inv_sigma, tgt[j * 3 + 1] * inv_sigma, tgt[j * 3 + 2] * inv_sigma, 0.f);
         }
         __syncthreads();
         // slice s takes elements s, s+4, ... of the tile: a fixed order, so y is reproducible
+        const int d0 = r0 - j0, d1 = r1 - j0;                 // tile positions of the two diagonal entries (if inside)
+#pragma unroll 4
         for (int t = slice; t < nj; t += MV_SLICES) {
             const float4 a = ta[t], c = tb[t];
-            const float ds = dist3(sx, sy, sz, a.x, a.y, a.z);
-            const float dt = dist3(tx, ty, tz, c.x, c.y, c.z);
-            const float m = (j0 + t == r) ? 0.f : compat_exact(ds, dt, sig2);
-            acc = fmaf(m, a.w, acc);
+            float2 dx = __fadd2_rn(sx, make_float2(-a.x, -a.x));
+            float2 dy = __fadd2_rn(sy, make_float2(-a.y, -a.y));
+            float2 dz = __fadd2_rn(sz, make_float2(-a.z, -a.z));
+            float2 q = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+            const float2 ds = make_float2(sm100::fast_sqrt(q.x), sm100::fast_sqrt(q.y));
+            dx = __fadd2_rn(tx, make_float2(-c.x, -c.x));
+            dy = __fadd2_rn(ty, make_float2(-c.y, -c.y));
+            dz = __fadd2_rn(tz, make_float2(-c.z, -c.z));
+            q = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+            const float2 dt = make_float2(sm100::fast_sqrt(q.x), sm100::fast_sqrt(q.y));
+            const float2 e = __fadd2_rn(ds, make_float2(-dt.x, -dt.y));
+            float2 m = make_float2(mv_fma_sat(-e.x, e.x, 1.0f), mv_fma_sat(-e.y, e.y, 1.0f));     // max(0, 1 - e^2)
+            if (t == d0) m.x = 0.f;
+            if (t == d1) m.y = 0.f;
+            acc = __ffma2_rn(m, make_float2(a.w, a.w), acc);
         }
     }
     part[slice][rl] = acc;
     __syncthreads();
-    if (slice == 0) csum[rl] = (part[0][rl] + part[1][rl]) + (part[2][rl] + part[3][rl]);
+    if (slice == 0) {
+        const float2 p0 = part[0][rl], p1 = part[1][rl], p2 = part[2][rl], p3 = part[3][rl];
+        csum[rl] = make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+    }
     cluster.sync();
-    if (ks == 0 && slice == 0 && r < row_end) {
-        float c[MV_KS];
+    if (ks == 0 && slice == 0) {
+        float2 c[MV_KS];
 #pragma unroll
         for (int k = 0; k < MV_KS; ++k) c[k] = cluster.map_shared_rank(csum, k)[rl];
-        y[r - row_begin] = ((c[0] + c[1]) + (c[2] + c[3])) + ((c[4] + c[5]) + (c[6] + c[7]));
+        if (r0 < row_end) y[r0 - row_begin] = ((c[0].x + c[1].x) + (c[2].x + c[3].x)) + ((c[4].x + c[5].x) + (c[6].x + c[7].x));
+        if (r1 < row_end) y[r1 - row_begin] = ((c[0].y + c[1].y) + (c[2].y + c[3].y)) + ((c[4].y + c[5].y) + (c[6].y + c[7].y));
     }
     cluster.sync();                                           // peers keep their shared memory until rank 0 has read it
 }
@@ -114,7 +146,7 @@ int launch_compat_matvec(const float* src, const float* tgt, const float* v, flo
     const int rows = row_end - row_begin;
     if (rows <= 0) return PDSC_OK;
     compat_matvec_kernel<<<dim3((rows + MV_ROWS - 1) / MV_ROWS, MV_KS), MV_THREADS, 0, st>>>(
-        src, tgt, v, y, N, row_begin, row_end, sigma_spat * sigma_spat, converged_flag);
+        src, tgt, v, y, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag);
     count_launches(1);
     return check_launch("compat_matvec");
 }
