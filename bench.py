@@ -385,7 +385,12 @@ def main():
                     "traffic": ncu_traffic(args), "traffic_note": "dram bytes of the main attention kernel per launch (ncu --set full, "
                     "profiles/r01_ncu_attn_pp.json); algorithmic HBM bytes per launch = 4*B*N*C*4", "peak_source": pk["source"] + ", bf16 sustained",
                     "algorithmic_flops_per_launch": flops_per_launch, "avg_launch_ms": avg_attn_ms,
-                    "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms}
+                    "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms,
+                    # split16 issues three fp16 products per contraction (hi*hi + hi*lo + lo*hi) to reach fp32-grade results:
+                    # the tensor pipe does 3x the algorithmic work, so `frac` cannot exceed 1/3
+                    "mma_terms": 1 if args.mode == "fp16" else (3 if args.mode == "split16" else 0),
+                    "issued": achieved * (3 if args.mode == "split16" else 1) if args.mode != "fp32" else None,
+                    "issued_frac": achieved * (3 if args.mode == "split16" else 1) / pk["bf16_sustained"] if args.mode != "fp32" else None}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",

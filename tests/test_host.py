@@ -75,3 +75,35 @@ def test_host_mlps_match_oracle(case, monkeypatch):
     assert (normed - g["normed_features"]).abs().max() < 2e-5
     scale = max(1.0, g["confidence"].abs().max().item())
     assert (conf - g["confidence"]).abs().max() < 1e-4 * scale
+
+
+def test_argument_errors_come_back_as_codes_without_a_gpu():
+    """Bad arguments are rejected before anything is launched: return code 1 and a message (SURVEY 8b error conventions)."""
+    lib = _cabi.load()
+    assert lib.pdsc_hybrid_search(None, 10, 0.1, 30, None, None, None, None, None, 0, None) == 1
+    assert b"hybrid_search" in lib.pdsc_last_error()
+    assert lib.pdsc_hybrid_search(1, 10, 0.1, 200, 1, None, None, None, 1, 0, None) == 1          # max_nn > 128
+    assert lib.pdsc_voxel_down_sample(None, None, 5, 0.05, None, None, None, None, 0, None) == 1
+    assert lib.pdsc_fpfh(None, None, 5, None, None, None, 100, None, None, None) == 1
+    assert lib.pdsc_nn_match_f64(1, 1, 5, 5, 100, 1, None, 1, 0, None) == 1                        # D > 64
+    assert lib.pdsc_icp_refine(None, None, None, 1, 10, 0.1, 30, 1e-6, 1e-6, None, None, None, None, 0, None) == 1
+    assert lib.pdsc_icp_refine(1, 1, 1, 1, 10, -0.1, 30, 1e-6, 1e-6, None, None, None, 1, 0, None) == 1
+    assert b"icp_refine" in lib.pdsc_last_error()
+    assert lib.pdsc_pick_seeds(None, None, 1, 10, 0.1, 1, None, None, None, None, 0, None) == 1
+
+
+def test_front_end_and_icp_refuse_cpu_tensors():
+    from pointdsc_b200 import benchmark_utils, frontend
+    pts = torch.rand(50, 3, dtype=torch.float64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        frontend.estimate_normal(pts, 0.1, 30)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        benchmark_utils.icp_refine(torch.rand(1, 20, 3), torch.rand(1, 20, 3), torch.eye(4)[None])
+
+
+def test_new_workspace_queries():
+    n = 258342
+    assert _cabi.workspace_bytes(_cabi.OP_HYBRID_SEARCH, N=n) >= n * 32
+    assert _cabi.workspace_bytes(_cabi.OP_VOXEL_DOWN_SAMPLE, N=n, S=1 << 20) >= (1 << 20) * 16 + n * 8
+    assert _cabi.workspace_bytes(_cabi.OP_NN_MATCH_F64, N=1000) >= 8 * 1000 * 16
+    assert _cabi.workspace_bytes(_cabi.OP_ICP_REFINE, B=16, N=5000) >= 16 * 5000 * 28
