@@ -38,7 +38,11 @@ def _cloud(kind, n, seed):
 
 @pytest.mark.parametrize("kind,n,radius,max_nn", [("uniform", 1, 0.1, 30), ("uniform", 2, 5.0, 30), ("uniform", 700, 0.15, 30),
                                                   ("uniform", 3000, 0.3, 100), ("float32_lattice", 1500, 0.11, 30),
-                                                  ("room", 6000, 0.1, 30), ("room", 2000, 0.25, 128)])
+                                                  ("room", 6000, 0.1, 30), ("room", 2000, 0.25, 128),
+                                                  # > 1024 candidates inside the radius: the warp-per-query kernel hands these
+                                                  # queries to the thread-per-query kernel
+                                                  ("uniform", 5000, 0.5, 64), ("float32_lattice", 4000, 0.3, 100),
+                                                  ("room", 70000, 0.05, 30)])
 def test_hybrid_search_bit_exact(kind, n, radius, max_nn):
     from pointdsc_b200 import _cabi
     pts = _cloud(kind, n, n)
