@@ -5,7 +5,8 @@
 // round trip (plus one more for the operand packing).  Here one CTA keeps a 128-row tile on chip through the
 // whole chain:
 //     x (+add_in) -> [ W_0, b_0, ReLU? ] -> ... -> [ W_{L-1}, b_{L-1}, ReLU? ] (+add_out) -> y
-//   thread t <-> row t: loads its fp32 row, splits it into fp16 hi + lo and stores both to TMEM as the A operand;
+//   threads t and t+128 <-> row t (alternate 32-column chunks, so that every scheduler has two warps to pick from):
+//   they load the fp32 row, split it into fp16 hi + lo and store both to TMEM as the A operand;
 //   an elected lane issues hi*hi + hi*lo + lo*hi tcgen05.mma against the pre-packed weights in shared memory
 //   (K-major, 128B swizzle, BatchNorm folded); the fp32 accumulator comes back through tcgen05.ld for bias / ReLU
 //   and is split again as the next layer's A operand.  Nothing but x and y touches HBM.
@@ -18,7 +19,7 @@ namespace pdsc {
 using namespace sm100;
 
 constexpr int ML_MAX_LAYERS = 3;
-constexpr int ML_THREADS = 128;
+constexpr int ML_THREADS = 256;     // two threads per row: thread t and t + 128 share row t & 127 and take alternate 32-column chunks
 constexpr uint32_t ML_A_LO = 64;      // TMEM columns: A hi [0,64), A lo [64,128), D [128,256)
 constexpr uint32_t ML_D = 128;
 
@@ -86,7 +87,8 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;      // a warp reaches the TMEM lanes of its quadrant (warp % 4)
+    const int rt = threadIdx.x & 127, half = threadIdx.x >> 7;         // row inside the tile, which chunks of it
     const long long n_tiles = (p.rows + 127) / 128;
     const int K0 = p.K[0], NL = p.N[p.n_layers - 1];
     // weights: one bulk copy per CTA (they stay resident while the CTA walks its row tiles); first tile's rows
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
 
     uint32_t mma_phase = 0;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long row = tile * 128 + threadIdx.x;
+        const long long row = tile * 128 + rt;
         const bool live = row < p.rows;
         const long long rrow = live ? row : p.rows - 1;
         const long long next = tile + gridDim.x;
@@ -119,9 +121,9 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
         if (p.add_out) ml_wait_group<1>(); else ml_wait_group<0>();
         __syncthreads();               // X(tile) has landed for every thread's copies
         {
-            const float4* xr = reinterpret_cast<const float4*>(xs + (uint32_t)threadIdx.x * ML_PITCH);
+            const float4* xr = reinterpret_cast<const float4*>(xs + (uint32_t)rt * ML_PITCH);
             const float4* ar = p.add_in ? reinterpret_cast<const float4*>(p.add_in + rrow * K0) : nullptr;
-            for (int c = 0; c < K0 / 32; ++c) {
+            for (int c = half; c < K0 / 32; c += 2) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -168,7 +170,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
             tc_fence_after();
             if (last && p.add_out) { ml_wait_group<1>(); __syncthreads(); }   // A(tile) has landed; X(next) may still fly
             const float* bias = bsm + p.b_off[l];
-            for (int c = 0; c < N / 32; ++c) {
+            for (int c = half; c < N / 32; c += 2) {
                 uint32_t r[32];
                 tmem_ld32(tmem + lane_addr + ML_D + (uint32_t)c * 32u, r);
                 tmem_ld_wait();
@@ -186,7 +188,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                     tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
                 } else {
                     // residual add in place in the stage; the finished fp32 row leaves through per-row bulk stores
-                    float4* orow = reinterpret_cast<float4*>(as + (uint32_t)threadIdx.x * ML_PITCH) + c * 8;
+                    float4* orow = reinterpret_cast<float4*>(as + (uint32_t)rt * ML_PITCH) + c * 8;
                     if (p.add_out) {
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
