@@ -9,7 +9,7 @@
 //   * hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM (fp32-grade accuracy);
 //   * the epilogue adds the bias (Q: also the log2(e)/sqrt(C) scale), splits again and assembles the finished 64 KB
 //     tile image in shared memory, which leaves as ONE bulk (TMA) store.
-// One CTA = one projection (blockIdx.y), walking the 128-row tiles of all pairs with two independent 4-warp groups
+// One CTA = one projection (blockIdx.y), walking the 128-row tiles of all pairs with two independent 8-warp groups
 // (own operand/image buffer, own accumulator columns, own barriers), so that the loads of one tile overlap the
 // MMAs / epilogue / store of another; the K CTAs also write the sigma-normalised key points.  Replaces: operand packing + library GEMM + attn_pp_prep_kernel.
 #include "common.cuh"
@@ -24,7 +24,8 @@ using namespace sm100;
 void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw);   // attn_pp.cu
 int attn_pp_tiles128(int N);
 
-constexpr int QK_THREADS = 256;       // two independent 4-warp groups per CTA (even / odd tiles) sharing the weights
+constexpr int QK_GROUP = 256;         // threads per group: two per row (thread t and t + 128 take alternate 32-column chunks of row t)
+constexpr int QK_THREADS = 2 * QK_GROUP;  // two independent 8-warp groups per CTA (even / odd tiles) sharing the weights
 constexpr uint32_t QK_BLK = 16384;        // one operand block: 128 rows x 64 fp16, 128-byte rows, 128B swizzle
 constexpr uint32_t QK_IMG = 4 * QK_BLK;   // hi blk0 | hi blk1 | lo blk0 | lo blk1
 constexpr uint32_t QK_PTS_FLOATS = 32 * 12 + 4;   // = PP_PTS_FLOATS (attn_pp.cu)
@@ -53,8 +54,9 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
     __shared__ float bsm[128];
     __shared__ uint64_t w_bar, mma_bars[2];
     __shared__ uint32_t tmem_base_s;
-    const int grp = threadIdx.x >> 7;     // warp group: tiles grp, grp + 2, ... of this CTA's share
-    const int warp = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31, tid = threadIdx.x & 127;
+    const int grp = threadIdx.x >> 8;     // warp group: tiles grp, grp + 2, ... of this CTA's share
+    const int warp = (threadIdx.x >> 5) & 7, lane = threadIdx.x & 31, gt = threadIdx.x & 255;
+    const int tid = gt & 127, half = gt >> 7;       // row of the tile this thread works on in the epilogue, and which chunks of it
     const int proj = blockIdx.y;          // 0 q, 1 k, 2 v
     // per group: the input tile as a tcgen05 operand (hi/lo, swizzled); after the MMAs the same buffer receives the
     // finished output tile image
@@ -73,13 +75,13 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s + (uint32_t)grp * 128u;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;      // TMEM lanes of the warp's quadrant (warp % 4)
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(&w_bar, QK_IMG);
         bulk_g2s(wsm, p.wpack + (size_t)proj * QK_IMG, QK_IMG / 2, &w_bar);
         bulk_g2s(wsm + QK_IMG / 2, p.wpack + (size_t)proj * QK_IMG + QK_IMG / 2, QK_IMG / 2, &w_bar);
     }
-    if (grp == 0) bsm[tid] = p.bias[proj * 128 + tid];
+    if (threadIdx.x < 128) bsm[threadIdx.x] = p.bias[proj * 128 + threadIdx.x];
     __syncthreads();
     mbar_wait_role(&w_bar, 0);
 
@@ -93,17 +95,17 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
         {
             const float* ybase = p.y + ((size_t)b * N + n0) * 128 + 4 * lane;
             const uint32_t blk = (uint32_t)(lane >> 4) * QK_BLK, chunk = (uint32_t)(lane & 15) >> 1, sub = (uint32_t)(lane & 1) * 8u;
-            float4 v[32];                  // the whole share of this warp is requested before any of it is used
+            float4 v[16];                  // the whole share of this warp is requested before any of it is used
 #pragma unroll
-            for (int u = 0; u < 32; ++u) {
-                const int r = warp + 4 * u;
+            for (int u = 0; u < 16; ++u) {
+                const int r = warp + 8 * u;
                 v[u] = (n0 + r < N) ? __ldg(reinterpret_cast<const float4*>(ybase + (size_t)r * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            if (tid == 0) bulk_wait_read();    // the image this buffer held (two tiles ago) has left shared memory
-            named_bar_sync(1 + grp, 128);
+            if (gt == 0) bulk_wait_read();     // the image this buffer held (two tiles ago) has left shared memory
+            named_bar_sync(1 + grp, QK_GROUP);
 #pragma unroll
-            for (int u = 0; u < 32; ++u) {
-                const uint32_t r = (uint32_t)(warp + 4 * u);
+            for (int u = 0; u < 16; ++u) {
+                const uint32_t r = (uint32_t)(warp + 8 * u);
                 uint32_t h0, l0, h1, l1;
                 qk_split_pair(v[u].x, v[u].y, h0, l0);
                 qk_split_pair(v[u].z, v[u].w, h1, l1);
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
         }
         fence_proxy_async();               // st.shared operand -> tensor-core (async proxy) reads
         tc_fence_before();
-        named_bar_sync(1 + grp, 128);      // operand complete; the group is done reading D of its previous tile
+        named_bar_sync(1 + grp, QK_GROUP); // operand complete; the group is done reading D of its previous tile
         // ---- 2. D = X W^T (q, k) or W X^T (v): hi*hi + hi*lo + lo*hi ----
         if (warp == 0) {
             tc_fence_after();
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
             }
             umma_commit_elect(&mma_bar);
         }
-        if (proj == 1) {
+        if (proj == 1 && half == 0) {
             // key points of this tile for the compatibility term (sigma-normalised, packed per key pair)
             const int n = min(n0 + tid, N - 1);
             const float* s = p.src + ((size_t)b * N + n) * 3;
@@ -148,13 +150,14 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
         mbar_wait(&mma_bar, mma_phase);
         mma_phase ^= 1;
         tc_fence_after();
-        named_bar_sync(1 + grp, 128);      // all MMAs have read the operand buffer: it may now receive the image
+        named_bar_sync(1 + grp, QK_GROUP); // all MMAs have read the operand buffer: it may now receive the image
         // ---- 3. epilogue: bias (+ scale), split, assemble the tile image ----
         {
             const float bias_t = bsm[tid];
             const bool row_live = n0 + tid < N;          // q, k: this thread's row exists
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int cc = 0; cc < 2; ++cc) {
+                const int c = 2 * cc + half;
                 uint32_t r[32];
                 tmem_ld32(tmem + lane_addr + (uint32_t)c * 32u, r);
                 tmem_ld_wait();
@@ -189,15 +192,15 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
         }
         fence_proxy_async();               // image written with st.shared, read by the bulk store
         tc_fence_before();
-        named_bar_sync(1 + grp, 128);
-        if (tid == 0) {
+        named_bar_sync(1 + grp, QK_GROUP);
+        if (gt == 0) {
             uint8_t* dst = (proj == 0 ? p.Qw : proj == 1 ? p.Kw : p.Vw) + (size_t)tile * QK_IMG;
             bulk_s2g(dst, img, QK_IMG / 2);
             bulk_s2g(dst + QK_IMG / 2, img + QK_IMG / 2, QK_IMG / 2);
             bulk_commit();
         }
     }
-    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x < 32) tmem_dealloc(tmem_base_s, 256);
