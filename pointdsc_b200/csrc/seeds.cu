@@ -243,82 +243,182 @@ __global__ void __launch_bounds__(KG_THREADS, 2) knn_dist_kernel(const float* __
 }
 
 // ------------------------------------------------------------------------------------------
-// seed kNN, stage 2: exact k smallest (dist, index) per seed row: 4-pass radix select on the
-// ordered bit pattern, ordered compaction of ties, rank sort of the k winners.
+// seed kNN, stage 2: exact k smallest (dist, index) per seed row.  One CTA per row:
+//   * the row is read from global memory ONCE, as ordered keys, into shared memory (rows of up to KS_SMEM_KEYS
+//     elements; longer rows are re-read from global memory, which L1/L2 serve); every thread keeps the minimum of
+//     the elements it staged;
+//   * fast path: the k-th smallest of the 128 thread minima is an upper bound of the k-th smallest element (the
+//     minima are k distinct elements below it), and only ~k * 1.2 elements of a row lie at or below it: they are
+//     compacted and rank-sorted by (key, index) directly -- exact, no histogram;
+//   * slow path (more than KS_CAND elements at or below the bound: heavy ties): 4-pass radix select on the keys.  Distances 2 - 2 cos sit in a narrow band, so the first passes put nearly every
+//     element into one bin: votes are aggregated per warp (__match_any_sync) before the shared-memory atomic;
+//   * one ordered pass: every thread owns a contiguous segment of the row, a block scan of the per-thread counts
+//     gives each thread its output slots ("< T" first, then the "== T" elements in index order);
+//   * rank sort of the k winners by (key, index).
 // ------------------------------------------------------------------------------------------
 constexpr int KS_THREADS = 128;
 constexpr int KS_MAXK = 64;
+constexpr int KS_SMEM_KEYS = 16384;
+constexpr int KS_CAND = 256;
 
+template <bool SMEM>
 __global__ void __launch_bounds__(KS_THREADS) knn_select_kernel(const float* __restrict__ D, int N, int S, int k,
                                                                 int64_t* __restrict__ knn_idx,
                                                                 float* __restrict__ knn_dist) {
+    extern __shared__ unsigned int keys[];          // SMEM: the row as ordered keys
     __shared__ unsigned int hist[256];
     __shared__ unsigned int sh_prefix, sh_want;
-    __shared__ unsigned int cand_key[KS_MAXK];
-    __shared__ int cand_idx[KS_MAXK];
-    __shared__ int n_less, n_eq_taken, warp_tot[KS_THREADS / 32];
+    __shared__ unsigned int cand_key[KS_CAND];
+    __shared__ int cand_idx[KS_CAND];
+    __shared__ __align__(16) unsigned int tmin[KS_THREADS];
+    __shared__ unsigned int sh_bound;
+    __shared__ int n_cand;
+    __shared__ int warp_less[KS_THREADS / 32], warp_eq[KS_THREADS / 32];
     const int row_id = blockIdx.x;   // b*S + s
     const float* row = D + (size_t)row_id * N;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    auto key_at = [&](int j) -> unsigned { return SMEM ? keys[j] : float_to_ordered(__ldg(row + j)); };
 
-    if (tid == 0) { sh_prefix = 0u; sh_want = (unsigned)k; n_less = 0; n_eq_taken = 0; }
+    unsigned my_min = 0xffffffffu;                   // above the key of +inf: a thread without elements ranks last
+#pragma unroll 8
+    for (int j = tid; j < N; j += KS_THREADS) {
+        const unsigned key = float_to_ordered(__ldcs(row + j));
+        if (SMEM) keys[j] = key;
+        my_min = min(my_min, key);
+    }
+    tmin[tid] = my_min;
+    if (tid == 0) { sh_prefix = 0u; sh_want = (unsigned)k; n_cand = 0; }
+    __syncthreads();
+    {
+        // rank of this thread's minimum among the 128 minima, ties broken by thread index (so ranks are distinct)
+        int rank = 0;
+#pragma unroll 8
+        for (int o4 = 0; o4 < KS_THREADS / 4; ++o4) {
+            const uint4 m = *reinterpret_cast<const uint4*>(&tmin[o4 * 4]);
+            const int o = o4 * 4;
+            rank += (m.x < my_min || (m.x == my_min && o < tid)) ? 1 : 0;
+            rank += (m.y < my_min || (m.y == my_min && o + 1 < tid)) ? 1 : 0;
+            rank += (m.z < my_min || (m.z == my_min && o + 2 < tid)) ? 1 : 0;
+            rank += (m.w < my_min || (m.w == my_min && o + 3 < tid)) ? 1 : 0;
+        }
+        if (rank == k - 1) sh_bound = my_min;        // k elements (thread minima) are <= this key
+    }
+    __syncthreads();
+    {
+        const unsigned bound = sh_bound;
+        if (my_min <= bound) {                       // only threads whose minimum passes can hold candidates
+            for (int j = tid; j < N; j += KS_THREADS) {
+                const unsigned key = key_at(j);
+                if (key <= bound) {
+                    const int p = atomicAdd(&n_cand, 1);
+                    if (p < KS_CAND) { cand_key[p] = key; cand_idx[p] = j; }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int nc = n_cand;
+    if (nc <= KS_CAND) {
+        // rank sort of the candidates by (key, index); the first k ranks are the answer
+        for (int c = tid; c < nc; c += KS_THREADS) {
+            const unsigned mk = cand_key[c];
+            const int mi = cand_idx[c];
+            int rank = 0;
+            for (int o = 0; o < nc; ++o) {
+                const unsigned ok = cand_key[o];
+                const int oi = cand_idx[o];
+                rank += (ok < mk || (ok == mk && oi < mi)) ? 1 : 0;
+            }
+            if (rank < k) {
+                knn_idx[(size_t)row_id * k + rank] = mi;
+                if (knn_dist) knn_dist[(size_t)row_id * k + rank] = row[mi];
+            }
+        }
+        return;
+    }
+    // ---- slow path: radix select ----
+    const int n_round = (N + KS_THREADS - 1) / KS_THREADS * KS_THREADS;     // whole warps take part in every vote
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
         for (int i = tid; i < 256; i += KS_THREADS) hist[i] = 0u;
         __syncthreads();
         const unsigned prefix = sh_prefix;
         const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        for (int j = tid; j < N; j += KS_THREADS) {
-            const unsigned key = float_to_ordered(row[j]);
-            if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        for (int j = tid; j < n_round; j += KS_THREADS) {
+            unsigned bin = 0xffffu;                                         // "no vote"
+            if (j < N) {
+                const unsigned key = key_at(j);
+                if ((key & himask) == prefix) bin = (key >> shift) & 255u;
+            }
+            const unsigned peers = __match_any_sync(0xffffffffu, bin);
+            if (bin != 0xffffu && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
         }
         __syncthreads();
-        if (tid == 0) {
-            unsigned want = sh_want, cum = 0u;
-            int bin = 0;
-            for (; bin < 256; ++bin) {
-                if (cum + hist[bin] >= want) break;
-                cum += hist[bin];
+        if (warp == 0) {
+            // bin of the want-th element: inclusive prefix sums of the 256 counts, 8 bins per lane
+            unsigned c[8], tot = 0u;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { c[i] = hist[lane * 8 + i]; tot += c[i]; }
+            unsigned incl = tot;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned o = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += o;
             }
-            sh_want = want - cum;
-            sh_prefix = prefix | ((unsigned)bin << shift);
+            const unsigned want = sh_want;
+            unsigned cum = incl - tot;                                      // elements in the bins of lower lanes
+            const bool here = cum < want && want <= incl;                   // exactly one lane
+            if (here) {
+                int i = 0;
+                for (; i < 7; ++i) {
+                    if (cum + c[i] >= want) break;
+                    cum += c[i];
+                }
+                sh_want = want - cum;
+                sh_prefix = prefix | ((unsigned)(lane * 8 + i) << shift);
+            }
         }
         __syncthreads();
     }
     const unsigned T = sh_prefix;           // key of the k-th smallest element
     const int want_eq = (int)sh_want;       // how many elements equal to T belong to the answer
     const int base_eq = k - want_eq;        // == number of elements with key < T
-    // ordered pass: "<T" appended with an atomic (order fixed later), "==T" taken in index order
-    for (int j0 = 0; j0 < N; j0 += KS_THREADS) {
-        const int j = j0 + tid;
-        unsigned key = 0xffffffffu;
-        if (j < N) key = float_to_ordered(row[j]);
-        const bool less = j < N && key < T;
-        const bool eq = j < N && key == T;
-        if (less) {
-            const int p = atomicAdd(&n_less, 1);
-            cand_key[p] = key;
-            cand_idx[p] = j;
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, eq);
-        if (lane == 0) warp_tot[warp] = __popc(m);
-        __syncthreads();
-        if (eq) {
-            int p = n_eq_taken + __popc(m & ((1u << lane) - 1u));
-            for (int w = 0; w < warp; ++w) p += warp_tot[w];
-            if (p < want_eq) {
-                cand_key[base_eq + p] = key;
-                cand_idx[base_eq + p] = j;
+    // ordered pass over contiguous segments (odd length: conflict-free shared-memory reads)
+    const int seg = ((N + KS_THREADS - 1) / KS_THREADS) | 1;
+    const int j_lo = min(tid * seg, N), j_hi = min(j_lo + seg, N);
+    int n_less = 0, n_eq = 0;
+    for (int j = j_lo; j < j_hi; ++j) {
+        const unsigned key = key_at(j);
+        n_less += key < T ? 1 : 0;
+        n_eq += key == T ? 1 : 0;
+    }
+    int less_incl = n_less, eq_incl = n_eq;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int a = __shfl_up_sync(0xffffffffu, less_incl, d), b = __shfl_up_sync(0xffffffffu, eq_incl, d);
+        if (lane >= d) { less_incl += a; eq_incl += b; }
+    }
+    if (lane == 31) { warp_less[warp] = less_incl; warp_eq[warp] = eq_incl; }
+    __syncthreads();
+    int less_off = less_incl - n_less, eq_off = eq_incl - n_eq;
+    for (int w = 0; w < warp; ++w) { less_off += warp_less[w]; eq_off += warp_eq[w]; }
+    if (n_less > 0 || (n_eq > 0 && eq_off < want_eq)) {
+        for (int j = j_lo; j < j_hi; ++j) {
+            const unsigned key = key_at(j);
+            if (key < T) {
+                cand_key[less_off] = key;
+                cand_idx[less_off] = j;
+                ++less_off;
+            } else if (key == T) {
+                if (eq_off < want_eq) {
+                    cand_key[base_eq + eq_off] = key;
+                    cand_idx[base_eq + eq_off] = j;
+                }
+                ++eq_off;
             }
         }
-        __syncthreads();
-        if (tid == 0) {
-            int tot = 0;
-            for (int w = 0; w < KS_THREADS / 32; ++w) tot += warp_tot[w];
-            n_eq_taken += tot;
-        }
-        __syncthreads();
     }
+    __syncthreads();
     // rank sort by (key, index)
     if (tid < k) {
         const unsigned mk = cand_key[tid];
@@ -353,7 +453,17 @@ int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int
     float* D = reinterpret_cast<float*>(ws);
     dim3 grid((N + KG_TJ - 1) / KG_TJ, (S + KG_TS - 1) / KG_TS, B);
     knn_dist_kernel<<<grid, KG_THREADS, 0, st>>>(normed, seeds, N, C, S, D);
-    knn_select_kernel<<<B * S, KS_THREADS, 0, st>>>(D, N, S, k, knn_idx, knn_dist);
+    if (N <= KS_SMEM_KEYS) {
+        const int smem = (int)sizeof(unsigned int) * N;
+        static int smem_set = 0;
+        if (smem > 40 * 1024 && smem > smem_set) {
+            cudaFuncSetAttribute(knn_select_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(unsigned int) * KS_SMEM_KEYS);
+            smem_set = (int)sizeof(unsigned int) * KS_SMEM_KEYS;
+        }
+        knn_select_kernel<true><<<B * S, KS_THREADS, smem, st>>>(D, N, S, k, knn_idx, knn_dist);
+    } else {
+        knn_select_kernel<false><<<B * S, KS_THREADS, 0, st>>>(D, N, S, k, knn_idx, knn_dist);
+    }
     count_launches(2);
     return check_launch("seed_knn");
 }

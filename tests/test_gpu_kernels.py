@@ -158,6 +158,40 @@ def test_seed_knn_vs_reference_golden(case):
     assert bool((dist[:, :, :-1] <= dist[:, :, 1:]).all())
 
 
+@pytest.mark.parametrize("N,copies", [(300, 4), (5000, 4), (20000, 4), (5000, 500), (20000, 1000)])
+def test_seed_knn_ties_and_long_rows(N, copies):
+    """Selection is exact under ties: every feature row appears `copies` times (bit-identical distances), so the
+    threshold group must be filled in index order (torch.topk-independent property of the reference's sort by
+    (distance, index)); N=20000 takes the variant that re-reads the row from global memory, and hundreds of copies
+    overflow the candidate list of the fast path (radix-select path)."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(N)
+    M, S, k = N // copies, 16, 40
+    base = torch.nn.functional.normalize(torch.randn(M, 128, generator=g), dim=-1)
+    feat = base.repeat(copies, 1)[None].contiguous()                  # row j == row j % M
+    seeds = torch.randperm(N, generator=g)[:S][None]
+    idx, dist = _cabi.seed_knn(cu(feat), cu(seeds), k, want_dist=True)
+    idx, dist = idx.cpu()[0], dist.cpu()[0]
+    full = 2 - 2 * (feat[0, seeds[0]].double() @ feat[0].double().T)  # [S, N]
+    for s in range(S):
+        me = int(seeds[0, s])
+        row, d = idx[s].tolist(), dist[s]
+        assert me not in row and len(set(row)) == k
+        assert bool((d[:-1] <= d[1:]).all())
+        same = d[:-1] == d[1:]
+        assert bool((idx[s][:-1][same] < idx[s][1:][same]).all()), "equal distances must come in index order"
+        kth = float(d[-1])
+        ref = full[s].clone()
+        ref[me] = float("inf")
+        must = set(torch.nonzero(ref < kth - 1e-5).flatten().tolist())
+        assert must <= set(row)
+        assert float(ref[row].max()) <= kth + 1e-5
+        chosen = set(row)
+        for j in row:                                                  # copies of the same feature row: lower indices first
+            for lower in range(j % M, j, M):
+                assert lower == me or lower in chosen, (s, j, lower)
+
+
 # ------------------------------------------------------------------------ (d) seed hypotheses
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_hypotheses_vs_reference_golden(case):
