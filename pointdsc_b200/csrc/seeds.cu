@@ -18,34 +18,49 @@ constexpr int NMS_TILE = 1024;
 __global__ void __launch_bounds__(NMS_THREADS) nms_kernel(const float* __restrict__ src,
                                                           const float* __restrict__ scores, int N, float T2,
                                                           int jchunk, int32_t* __restrict__ suppressed) {
-    __shared__ float4 tile[NMS_TILE];
+    // two candidates per entry, coordinates negated: (-x_j, -x_j+1, -y_j, -y_j+1) and (-z_j, -z_j+1, score_j, score_j+1),
+    // so that the distance runs on packed f32x2 instructions (each lane rounded like the scalar op: same bits)
+    __shared__ float4 tile_a[NMS_TILE / 2], tile_b[NMS_TILE / 2];
     const int b = blockIdx.z;
     const float* sb = src + (size_t)b * N * 3;
     const float* cb = scores + (size_t)b * N;
     const int i = blockIdx.x * NMS_THREADS + threadIdx.x;
     float xi = 0.f, yi = 0.f, zi = 0.f, si = 0.f;
     if (i < N) { xi = sb[i * 3]; yi = sb[i * 3 + 1]; zi = sb[i * 3 + 2]; si = cb[i]; }
+    const float2 xi2 = make_float2(xi, xi), yi2 = make_float2(yi, yi), zi2 = make_float2(zi, zi);
     const int j_begin = blockIdx.y * jchunk;
     const int j_end = min(N, j_begin + jchunk);
-    bool sup = false;
+    bool keep = true;
     for (int j0 = j_begin; j0 < j_end; j0 += NMS_TILE) {
         const int nj = min(NMS_TILE, j_end - j0);
+        const int nj2 = (nj + 1) >> 1;
         __syncthreads();
-        for (int t = threadIdx.x; t < nj; t += NMS_THREADS) {
-            const int j = j0 + t;
-            tile[t] = make_float4(sb[j * 3], sb[j * 3 + 1], sb[j * 3 + 2], cb[j]);
+        for (int t = threadIdx.x; t < nj2; t += NMS_THREADS) {
+            const int j = j0 + 2 * t;
+            const bool two = 2 * t + 1 < nj;
+            // an odd tail is padded with a point nothing is close to (d2 overflows to +inf) and the lowest score
+            const float x1 = two ? sb[j * 3 + 3] : 3.0e38f, y1 = two ? sb[j * 3 + 4] : 3.0e38f, z1 = two ? sb[j * 3 + 5] : 3.0e38f;
+            tile_a[t] = make_float4(-sb[j * 3], -x1, -sb[j * 3 + 1], -y1);
+            tile_b[t] = make_float4(-sb[j * 3 + 2], -z1, cb[j], two ? cb[j + 1] : -INFINITY);
         }
         __syncthreads();
 #pragma unroll 4
-        for (int t = 0; t < nj; ++t) {
-            const float4 p = tile[t];
+        for (int t = 0; t < nj2; ++t) {
+            const float4 pa = tile_a[t], pb = tile_b[t];
             // sqrt(d2) >= R  <=>  d2 >= T2 (T2 = smallest fp32 whose correctly rounded sqrt reaches R, found on
             // the host), with d2 rounded exactly like torch.norm's mul/add sequence: no sqrt in the loop
-            const float dx = xi - p.x, dy = yi - p.y, dz = zi - p.z;
-            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-            sup |= (!(si >= p.w)) & (!(d2 >= T2));   // negated forms keep the reference's NaN behaviour
+            const float2 dx = __fadd2_rn(xi2, make_float2(pa.x, pa.y));
+            const float2 dy = __fadd2_rn(yi2, make_float2(pa.z, pa.w));
+            const float2 dz = __fadd2_rn(zi2, make_float2(pb.x, pb.y));
+            // the sums stay scalar: ptxas (12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2, which would change the rounding
+            const float2 qx = __fmul2_rn(dx, dx), qy = __fmul2_rn(dy, dy), qz = __fmul2_rn(dz, dz);
+            const float2 d2 = make_float2(__fadd_rn(__fadd_rn(qx.x, qy.x), qz.x), __fadd_rn(__fadd_rn(qx.y, qy.y), qz.y));
+            // suppressed by j  <=>  !(score_i >= score_j) && !(d2 >= T2)   (negated forms keep the reference's NaN behaviour)
+            keep = keep && ((si >= pb.z) || (d2.x >= T2));
+            keep = keep && ((si >= pb.w) || (d2.y >= T2));
         }
     }
+    const bool sup = !keep;
     if (sup && i < N) suppressed[(size_t)b * N + i] = 1;
 }
 
