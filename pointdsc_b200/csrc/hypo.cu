@@ -118,26 +118,30 @@ __global__ void __launch_bounds__(HY_THREADS) seed_hypo_kernel(
         }
     }
     __syncthreads();
-    // total_knn_M = feature_knn_M * spatial_knn_M, zero diagonal (models/PointDSC.py:258-278);
-    // upper-triangular 4x4 register blocks, mirrored on store
+    // total_knn_M = feature_knn_M * spatial_knn_M, zero diagonal (models/PointDSC.py:258-278).
+    // The k x k matrix is cut into upper-triangular 4 x 4 blocks, mirrored on store; a block is two work items of
+    // 2 x 4 outputs, so that all four warps take part.  Block q owns rows q, q + kb, q + 2 kb, q + 3 kb: neighbouring
+    // threads (neighbouring bj) then read neighbouring feature rows, which the row pitch of C + 4 floats spreads over
+    // all banks (rows 4 q .. 4 q + 3 per block would put every second block on the same banks).
     const int kb = kp >> 2;
     const int nblk = kb * (kb + 1) / 2;
-    for (int blk = tid; blk < nblk; blk += HY_THREADS) {
+    for (int item = tid; item < 2 * nblk; item += HY_THREADS) {
+        const int blk = item >> 1, half = item & 1;
         int bi = 0, rem = blk;
         while (rem >= kb - bi) { rem -= kb - bi; ++bi; }
         const int bj = bi + rem;
-        float acc[4][4] = {};
-        const float* Fa = F + (size_t)(bi * 4) * ldf;
-        const float* Fb = F + (size_t)(bj * 4) * ldf;
+        float acc[2][4] = {};
+        const float* Fa = F + (size_t)(bi + kb * 2 * half) * ldf;
+        const float* Fb = F + (size_t)bj * ldf;
+        const size_t rstep = (size_t)kb * ldf;
         for (int c = 0; c < C; c += 4) {
-            float4 av[4], bv[4];
+            float4 av[2], bv[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                av[i] = *reinterpret_cast<const float4*>(Fa + (size_t)i * ldf + c);
-                bv[i] = *reinterpret_cast<const float4*>(Fb + (size_t)i * ldf + c);
-            }
+            for (int i = 0; i < 2; ++i) av[i] = *reinterpret_cast<const float4*>(Fa + i * rstep + c);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 4; ++j) bv[j] = *reinterpret_cast<const float4*>(Fb + j * rstep + c);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     acc[i][j] = fmaf(av[i].x, bv[j].x, acc[i][j]);
@@ -147,10 +151,10 @@ __global__ void __launch_bounds__(HY_THREADS) seed_hypo_kernel(
                 }
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const int ra = bi * 4 + i, rb = bj * 4 + j;
+                const int ra = bi + kb * (2 * half + i), rb = bj + kb * j;
                 if (ra >= k || rb >= k) continue;
                 float m = 0.f;
                 if (ra != rb) {
