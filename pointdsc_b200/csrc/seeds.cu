@@ -6,6 +6,7 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 namespace pdsc {
 
@@ -449,7 +450,11 @@ __global__ void __launch_bounds__(KS_THREADS) knn_select_kernel(const float* __r
     }
 }
 
-size_t seed_knn_workspace(int B, int N, int S) { return sizeof(float) * (size_t)B * S * N; }
+size_t knn_tc_image_bytes(int B, int S);                                                                        // knn_tc.cu
+int launch_knn_gram_tc(const float* normed, const int64_t* seeds, int B, int N, int S, float* D, void* img, cudaStream_t st);
+
+// distances [B][S][N] | seed operand images of the tensor-core Gram
+size_t seed_knn_workspace(int B, int N, int S) { return align_up(sizeof(float) * (size_t)B * S * N, 1024) + knn_tc_image_bytes(B, S); }
 
 int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int C, int S, int k,
                     int64_t* knn_idx, float* knn_dist, void* ws, size_t ws_bytes, cudaStream_t st) {
@@ -466,8 +471,18 @@ int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int
         return PDSC_ERR_WORKSPACE;
     }
     float* D = reinterpret_cast<float*>(ws);
-    dim3 grid((N + KG_TJ - 1) / KG_TJ, (S + KG_TS - 1) / KG_TS, B);
-    knn_dist_kernel<<<grid, KG_THREADS, 0, st>>>(normed, seeds, N, C, S, D);
+    // C == 128: Gram on the tensor cores (knn_tc.cu); PDSC_KNN_FP32=1 keeps the fp32 CUDA-core Gram (tests compare the two)
+    const char* env_fp32 = getenv("PDSC_KNN_FP32");
+    const bool force_fp32 = env_fp32 && atoi(env_fp32) != 0;
+    if (C == 128 && !force_fp32) {
+        void* img = reinterpret_cast<char*>(ws) + align_up(sizeof(float) * (size_t)B * S * N, 1024);
+        const int rc = launch_knn_gram_tc(normed, seeds, B, N, S, D, img, st);
+        if (rc != PDSC_OK) return rc;
+    } else {
+        dim3 grid((N + KG_TJ - 1) / KG_TJ, (S + KG_TS - 1) / KG_TS, B);
+        knn_dist_kernel<<<grid, KG_THREADS, 0, st>>>(normed, seeds, N, C, S, D);
+        count_launches(1);
+    }
     if (N <= KS_SMEM_KEYS) {
         const int smem = (int)sizeof(unsigned int) * N;
         static int smem_set = 0;
@@ -479,7 +494,7 @@ int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int
     } else {
         knn_select_kernel<false><<<B * S, KS_THREADS, 0, st>>>(D, N, S, k, knn_idx, knn_dist);
     }
-    count_launches(2);
+    count_launches(1);
     return check_launch("seed_knn");
 }
 

@@ -192,6 +192,31 @@ def test_seed_knn_ties_and_long_rows(N, copies):
                 assert lower == me or lower in chosen, (s, j, lower)
 
 
+@pytest.mark.parametrize("N,S", [(5000, 500), (1000, 100), (777, 300), (10000, 1000)])
+def test_seed_knn_tensor_core_gram_vs_fp32_gram(N, S, monkeypatch):
+    """The tcgen05 Gram (fp16 hi/lo split, fp32 accumulate) against the fp32 CUDA-core Gram of the same library:
+    distances within 2e-6, neighbour lists equal except where the fp32 distances are closer than that."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(N + S)
+    feat = torch.nn.functional.normalize(torch.randn(2, N, 128, generator=g), dim=-1)
+    seeds = torch.stack([torch.randperm(N, generator=g)[:S] for _ in range(2)])
+    k = 40
+    idx_tc, d_tc = _cabi.seed_knn(cu(feat), cu(seeds), k, want_dist=True)
+    monkeypatch.setenv("PDSC_KNN_FP32", "1")
+    idx_32, d_32 = _cabi.seed_knn(cu(feat), cu(seeds), k, want_dist=True)
+    monkeypatch.delenv("PDSC_KNN_FP32")
+    idx_tc, d_tc, idx_32, d_32 = idx_tc.cpu(), d_tc.cpu(), idx_32.cpu(), d_32.cpu()
+    assert float((d_tc - d_32).abs().max()) < 2e-6
+    assert not (idx_tc == seeds[:, :, None]).any()
+    full = 2 - 2 * torch.einsum("bsc,bnc->bsn", torch.gather(feat, 1, seeds[:, :, None].expand(-1, -1, 128)).double(), feat.double())
+    differ = (idx_tc != idx_32)
+    if differ.any():
+        a = torch.gather(full, 2, idx_tc)[differ]
+        c = torch.gather(full, 2, idx_32)[differ]
+        assert float((a - c).abs().max()) < 2e-6, "lists may differ only by near-ties"
+    assert float(differ.float().mean()) < 0.01
+
+
 # ------------------------------------------------------------------------ (d) seed hypotheses
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_hypotheses_vs_reference_golden(case):

@@ -25,7 +25,8 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_workspace_queries_do_not_need_a_gpu():
-    assert _cabi.workspace_bytes(_cabi.OP_SEED_KNN, B=2, N=1000, C=128, S=100, k=40) == 2 * 100 * 1000 * 4
+    need = _cabi.workspace_bytes(_cabi.OP_SEED_KNN, B=2, N=1000, C=128, S=100, k=40)      # distances + seed operand images
+    assert 2 * 100 * 1000 * 4 + 2 * 131072 <= need <= 2 * 100 * 1000 * 4 + 2 * 131072 + 1024
     assert _cabi.workspace_bytes(_cabi.OP_PICK_SEEDS, B=1, N=5000) >= 5000 * 4
     assert _cabi.workspace_bytes(_cabi.OP_PICK_SEEDS, B=1, N=50000) >= 65536 * 8
 
