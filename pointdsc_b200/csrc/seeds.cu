@@ -93,12 +93,14 @@ __global__ void __launch_bounds__(1024) seed_order_kernel(const float* __restric
                                                           uint8_t* __restrict__ is_local_max,
                                                           int32_t* __restrict__ n_pos) {
     extern __shared__ unsigned long long sbuf[];
-    __shared__ int pos_count;
+    __shared__ unsigned long long cand[1024];     // thread minima, then the candidates of the short sort
+    __shared__ int pos_count, n_cand;
     const int b = blockIdx.x;
     unsigned long long* a = gbuf ? gbuf + (size_t)b * n_pow2 : sbuf;
-    if (threadIdx.x == 0) pos_count = 0;
+    if (threadIdx.x == 0) { pos_count = 0; n_cand = 0; }
     __syncthreads();
     int local_pos = 0;
+    unsigned long long my_min = ~0ull;
     for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
         unsigned long long key = ~0ull;  // padding sorts last
         if (i < N) {
@@ -110,11 +112,41 @@ __global__ void __launch_bounds__(1024) seed_order_kernel(const float* __restric
             if (is_local_max) is_local_max[(size_t)b * N + i] = lm ? 1 : 0;
         }
         a[i] = key;
+        my_min = key < my_min ? key : my_min;
     }
     local_pos = warp_sum(local_pos);
     if ((threadIdx.x & 31) == 0 && local_pos) atomicAdd(&pos_count, local_pos);
-    bitonic_sort(a, n_pow2);
-    for (int s = threadIdx.x; s < S; s += blockDim.x) seeds[(size_t)b * S + s] = (int64_t)(a[s] & 0xffffffffull);
+    // Short path: only the S first keys are wanted.  The S-th smallest of the 1024 per-thread minima is an upper bound of
+    // the S-th smallest key (the minima are S distinct keys at or below it); the few keys at or below the bound
+    // (about S * 1.3) are sorted instead of all n_pow2.  Same result as the full sort: keys are distinct.
+    bool done = false;
+    if (blockDim.x == 1024 && S <= 1024 && S <= N) {
+        cand[threadIdx.x] = my_min;
+        bitonic_sort(cand, 1024);
+        const unsigned long long bound = cand[S - 1];
+        __syncthreads();                                   // everyone has the bound: cand may be overwritten
+        if (bound != ~0ull) {
+            for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
+                const unsigned long long key = a[i];
+                if (key <= bound) {
+                    const int pos = atomicAdd(&n_cand, 1);
+                    if (pos < 1024) cand[pos] = key;
+                }
+            }
+            __syncthreads();
+            const int nc = n_cand;
+            if (nc <= 1024) {
+                if ((int)threadIdx.x >= nc) cand[threadIdx.x] = ~0ull;
+                bitonic_sort(cand, 1024);
+                for (int s = threadIdx.x; s < S; s += blockDim.x) seeds[(size_t)b * S + s] = (int64_t)(cand[s] & 0xffffffffull);
+                done = true;
+            }
+        }
+    }
+    if (!done) {
+        bitonic_sort(a, n_pow2);
+        for (int s = threadIdx.x; s < S; s += blockDim.x) seeds[(size_t)b * S + s] = (int64_t)(a[s] & 0xffffffffull);
+    }
     if (threadIdx.x == 0 && n_pos) n_pos[b] = pos_count;
 }
 
