@@ -133,6 +133,27 @@ def test_pick_seeds_large_n_global_sort_path():
     assert float(sk[-1]) >= float(torch.sort(keys, descending=True)[0][S - 1])
 
 
+@pytest.mark.parametrize("N,S,mode", [(20000, 500, "random"), (5000, 500, "all_equal"), (5000, 1024, "random"),
+                                      (3000, 1500, "random"), (700, 70, "mostly_negative")])
+def test_pick_seeds_order_short_and_full_sort_paths(N, S, mode):
+    """The seed order is (key descending, index ascending) whichever path sorts it: the bounded short sort (S <= 1024),
+    the full sort (S > 1024), keys in shared or global memory (N > 16384), ties everywhere (equal scores)."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(N + S)
+    src = torch.rand(1, N, 3, generator=g) * 50
+    conf = torch.randn(1, N, generator=g)
+    if mode == "all_equal":
+        conf = torch.full((1, N), 0.25)
+    elif mode == "mostly_negative":
+        conf = conf - 2.0
+    seeds, lm, npos = _cabi.pick_seeds(cu(src), cu(conf), 0.6, S, want_aux=True)
+    keys = conf[0] * lm[0].cpu().float()
+    keys[keys == 0] = 0.0
+    order = sorted(range(N), key=lambda i: (-float(keys[i]), i))[:S]
+    assert seeds[0].cpu().tolist() == order
+    assert int(npos[0]) == int((keys > 0).sum())
+
+
 # --------------------------------------------------------------------------------- (c) seed kNN
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_knn_vs_reference_golden(case):
