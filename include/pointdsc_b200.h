@@ -166,6 +166,17 @@ int pdsc_post_refine(float* trans_inout, const float* src, const float* tgt, int
                      float tau, int max_iter, int32_t* iters_out, int32_t* counts_out,
                      void* stream);
 
+/* Feature head: the two consumers of corr_features right after the encoder, in one pass over the rows --
+ *  normed = F.normalize(corr_features, p=2, dim=1) (models/PointDSC.py:156; x / max(||x||_2, eps), eps = 1e-12) and
+ *  confidence = self.classification(corr_features) (models/PointDSC.py:107-113 Conv1d C->H1, ReLU, H1->H2, ReLU, H2->1,
+ *  called at :171).  feat fp32 [rows, C] channel-last; w1t [C,H1], w2t [H1,H2] (y = x @ wt), w3 [H2], b3 [1];
+ *  normed_out fp32 [rows, C], conf_out fp32 [rows].  Built for C=128, H1=H2=32 (the reference's sizes); other
+ *  sizes return PDSC_ERR_ARG (the Python host keeps torch ops for them). */
+int pdsc_feature_head(const float* feat, int64_t rows, int C, int H1, int H2,
+                      const float* w1t, const float* b1, const float* w2t, const float* b2,
+                      const float* w3, const float* b3, float eps,
+                      float* normed_out, float* conf_out, void* stream);
+
 /* (b) full-matrix power iteration building block; cal_leading_eigenvector
  *  models/PointDSC.py:338-358 applied to the N x N compatibility matrix with zero diagonal
  *  (the call kept at models/PointDSC.py:170; baseline_scripts/baseline_3DMatch.py:19-46).

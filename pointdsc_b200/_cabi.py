@@ -40,6 +40,8 @@ SIGNATURES = {
                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_post_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p,
                                  c_void_p]),
+    "pdsc_feature_head": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_float, c_void_p, c_void_p, c_void_p]),
     "pdsc_split16_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "pdsc_qkv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_size_t,
                               c_void_p]),
@@ -338,6 +340,21 @@ def post_refine(trans, src, tgt, tau, max_iter=20, want_aux=False):
     _check(rc, "pdsc_post_refine")
     _count()
     return (trans, iters, counts) if want_aux else trans
+
+
+def feature_head(feat, w1t, b1, w2t, b2, w3, b3, eps=1e-12):
+    """feat [B,N,C] -> (F.normalize(feat, dim=-1) [B,N,C], classifier logits [B,N]); models/PointDSC.py:156,171."""
+    lib = load()
+    B, N, C = feat.shape
+    normed = torch.empty_like(feat)
+    conf = torch.empty(B, N, dtype=torch.float32, device=feat.device)
+    rc = lib.pdsc_feature_head(_ptr(feat, torch.float32, "feat"), B * N, C, int(w1t.shape[1]), int(w2t.shape[1]),
+                               _ptr(w1t, torch.float32, "w1t"), _ptr(b1, torch.float32, "b1"), _ptr(w2t, torch.float32, "w2t"),
+                               _ptr(b2, torch.float32, "b2"), _ptr(w3, torch.float32, "w3"), _ptr(b3, torch.float32, "b3"),
+                               float(eps), normed.data_ptr(), conf.data_ptr(), _stream())
+    _check(rc, "pdsc_feature_head")
+    _count()
+    return normed, conf
 
 
 def compat_matvec(src, tgt, v, row_begin, row_end, sigma_spat, converged_flag=None, out=None):

@@ -220,6 +220,15 @@ int pdsc_post_refine(float* trans_inout, const float* src, const float* tgt, int
                               reinterpret_cast<cudaStream_t>(stream));
 }
 
+int pdsc_feature_head(const float* feat, int64_t rows, int C, int H1, int H2, const float* w1t, const float* b1, const float* w2t,
+                      const float* b2, const float* w3, const float* b3, float eps, float* normed_out, float* conf_out, void* stream) {
+    PDSC_REQUIRE(feat && w1t && b1 && w2t && b2 && w3 && b3 && normed_out && conf_out, "feature_head: null pointer");
+    PDSC_REQUIRE(rows > 0, "feature_head: bad row count");
+    PDSC_REQUIRE(aligned16(feat) && aligned16(normed_out) && aligned16(w1t) && aligned16(w2t), "feature_head: pointers must be 16-byte aligned");
+    return launch_feature_head(feat, rows, C, H1, H2, w1t, b1, w2t, b2, w3, b3, eps, normed_out, conf_out,
+                               reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_split16_rows(const float* x, const float* add, float* y_out, void* out16, int64_t rows, int K, int Kp, int relu,
                       void* stream) {
     PDSC_REQUIRE(x && out16, "split16_rows: null pointer");

@@ -183,6 +183,8 @@ int launch_score_hypotheses(const float* seed_trans, const float* src, const flo
                             float* final_labels, cudaStream_t st);
 int launch_post_refine(float* trans, const float* src, const float* tgt, int B, int N, float tau, int max_iter,
                        int32_t* iters_out, int32_t* counts_out, cudaStream_t st);
+int launch_feature_head(const float* feat, long long rows, int C, int H1, int H2, const float* w1t, const float* b1, const float* w2t,
+                        const float* b2, const float* w3, const float* b3, float eps, float* normed, float* conf, cudaStream_t st);
 size_t pick_seeds_workspace(int B, int N);
 int launch_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds,
                       uint8_t* is_local_max, int32_t* n_pos, void* ws, size_t ws_bytes, cudaStream_t st);

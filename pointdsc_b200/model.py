@@ -170,6 +170,8 @@ class PointDSC(nn.Module):
             layers.append(L)
         P["layers"] = layers
         P["cls"] = [_fold(self.classification[i], None) for i in (0, 2, 4)]
+        P["cls"] = [(W.contiguous(), b.contiguous()) for W, b in P["cls"]]
+        P["cls_w3"] = P["cls"][2][0].reshape(-1).contiguous()
         # one host sync at pack time instead of one per forward
         P["sigma"] = float(self.sigma.detach().float().item())
         P["sigma_spat"] = float(self.sigma_spat.detach().float().item())
@@ -275,8 +277,14 @@ class PointDSC(nn.Module):
         torch.backends.cuda.matmul.allow_tf32 = False   # the MLPs must stay fp32 for parity
         try:
             feat = self.encode(corr_pos, src, tgt)
-            normed = F.normalize(feat, p=2, dim=-1)                      # :156
-            confidence = self.classify(feat)                             # :171
+            cls = P["cls"]
+            if feat.shape[-1] == 128 and cls[0][0].shape[1] == 32 and cls[1][0].shape[1] == 32 and self.mlp_mode == "fused":
+                # one pass over the features: normalisation (:156) + classifier (:171)
+                normed, confidence = _cabi.feature_head(feat.contiguous(), cls[0][0], cls[0][1], cls[1][0], cls[1][1],
+                                                        P["cls_w3"], cls[2][1])
+            else:
+                normed = F.normalize(feat, p=2, dim=-1)                      # :156
+                confidence = self.classify(feat)                             # :171
         finally:
             torch.backends.cuda.matmul.allow_tf32 = prev_tf32
         ws = self._ws

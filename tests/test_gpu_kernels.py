@@ -154,6 +154,27 @@ def test_pick_seeds_order_short_and_full_sort_paths(N, S, mode):
     assert int(npos[0]) == int((keys > 0).sum())
 
 
+@pytest.mark.parametrize("B,N", [(1, 5), (2, 777), (3, 4096)])
+def test_feature_head_vs_torch(B, N):
+    """pdsc_feature_head = F.normalize (models/PointDSC.py:156) + the classifier (:107-113,:171) in one pass; against
+    the same operations in torch fp32 (tolerance 1e-6 relative to the largest logit: the summation order differs)."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(B * 1000 + N)
+    feat = torch.randn(B, N, 128, generator=g) * 3
+    feat[0, 0] = 0.0                                       # zero row: x / max(0, eps) = 0
+    w1, b1 = torch.randn(128, 32, generator=g) * 0.1, torch.randn(32, generator=g)
+    w2, b2 = torch.randn(32, 32, generator=g) * 0.2, torch.randn(32, generator=g)
+    w3, b3 = torch.randn(32, generator=g) * 0.3, torch.randn(1, generator=g)
+    normed, conf = _cabi.feature_head(cu(feat), cu(w1), cu(b1), cu(w2), cu(b2), cu(w3), cu(b3))
+    ref_n = torch.nn.functional.normalize(feat.double(), p=2, dim=-1)
+    h = torch.relu(feat.double() @ w1.double() + b1.double())
+    h = torch.relu(h @ w2.double() + b2.double())
+    ref_c = h @ w3.double() + b3.double()
+    assert float((normed.cpu().double() - ref_n).abs().max()) < 2e-7
+    assert float((conf.cpu().double() - ref_c).abs().max()) < 1e-6 * max(1.0, float(ref_c.abs().max())) * 4
+    assert bool((normed[0, 0] == 0).all())
+
+
 # --------------------------------------------------------------------------------- (c) seed kNN
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_knn_vs_reference_golden(case):
