@@ -91,9 +91,12 @@ __global__ void __launch_bounds__(256) attn_pp_prep_kernel(const float* __restri
                                                            const float* __restrict__ src, const float* __restrict__ tgt,
                                                            int N, int NT128, float qscale, float inv_sigma,
                                                            uint8_t* __restrict__ Qw, uint8_t* __restrict__ Kw,
-                                                           uint8_t* __restrict__ Vw, float* __restrict__ Pw) {
+                                                           uint8_t* __restrict__ Vw, float* __restrict__ Pw,
+                                                           int* __restrict__ counters, int n_counters) {
     extern __shared__ __align__(16) float vt[];   // [128 keys][129] staging for the V transpose
     const int t = blockIdx.x, b = blockIdx.y;
+    if (t == 0 && b == 0)                         // arrival counters of the main kernel start at zero
+        for (int i = threadIdx.x; i < n_counters; i += blockDim.x) counters[i] = 0;
     const int n0 = t * PP_SUB;
     const size_t tile = (size_t)b * NT128 + t;
     uint8_t* qd = Qw + tile * PP_QTILE_BYTES;
@@ -766,6 +769,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 const int c_first = (int)(((x0 + 1) * G + T - 1) / T) - 1;
                 const int c_last = (int)(((x0 + NT) * G + T - 1) / T) - 1;
                 if (last_flag[x] == c_last - c_first) {
+                    // last arrival: leave the counter at zero for the next launch on this workspace
+                    if ((warp & 7) == 0 && lane == 0) p.counters[((size_t)b * p.NRBp + rb) * 2 + x] = 0;
                     __threadfence();
                     float M = -INFINITY;
                     for (int c = c_first; c <= c_last; ++c) {
@@ -851,7 +856,7 @@ static int pp_grid(int B, int NU, int NT, int CL) {
 }
 
 struct PpLayout {
-    size_t q, k, v, pts, part_o, part_ml, chain_o, chain_m, counters, total;
+    size_t q, k, v, pts, part_o, part_ml, chain_o, chain_m, counters, n_counters, total;
 };
 static PpLayout pp_layout(int B, int N) {
     const int NRB = (N + PP_BM - 1) / PP_BM, NT = (N + PP_BN - 1) / PP_BN;
@@ -870,6 +875,7 @@ static PpLayout pp_layout(int B, int N) {
     L.chain_o = off; off += (NT > 100 || getenv("PDSC_ATTN_CHAIN") ? (size_t)PP_CHAIN_SLOTS : 0) * G * 2 * PP_SUB * PP_C * sizeof(float);
     L.chain_m = off; off += (size_t)PP_CHAIN_SLOTS * G * 2 * PP_SUB * sizeof(float);
     L.counters = off; off += align_up((size_t)B * NRBp * 2 * sizeof(int), 1024);
+    L.n_counters = (size_t)B * NRBp * 2;
     L.total = off + 1024;
     return L;
 }
@@ -877,11 +883,16 @@ static PpLayout pp_layout(int B, int N) {
 size_t attn_pp_workspace(int B, int N) { return pp_layout(B, N).total; }
 int attn_pp_tiles128(int N) { return 2 * ((((N + PP_BM - 1) / PP_BM) + 1) & ~1); }   // 128-row tiles per pair in the workspace
 
-void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw) {
+// counters / n_counters: the stream-K arrival counters of the main kernel.  Whoever writes the operand tiles (qkv_pack_kernel,
+// attn_pp_prep_kernel) also zeroes them -- no separate memset on the stream; the main kernel leaves them at zero again.
+void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw, int** counters,
+                           int* n_counters) {
     const PpLayout L = pp_layout(B, N);
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
     *Qw = base + L.q; *Kw = base + L.k; *Vw = base + L.v;
     *Pw = reinterpret_cast<float*>(base + L.pts);
+    *counters = reinterpret_cast<int*>(base + L.counters);
+    *n_counters = (int)(L.n_counters);
 }
 
 // Main kernel on operand tiles already present in the workspace (written by attn_pp_prep_kernel or qkv_pack_kernel).
@@ -938,7 +949,6 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
         attr_set = true;
     }
     const int G = pp_grid(B, p.NU, NT, CL);
-    cudaMemsetAsync(p.counters, 0, (size_t)B * NRBp * 2 * sizeof(int), st);
     p.trace = nullptr;
     const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
     if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
@@ -988,7 +998,9 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
     const int NT128 = attn_pp_tiles128(N);
     uint8_t *Qw, *Kw, *Vw;
     float* Pw;
-    attn_pp_tile_pointers(ws, B, N, &Qw, &Kw, &Vw, &Pw);
+    int* counters;
+    int n_counters;
+    attn_pp_tile_pointers(ws, B, N, &Qw, &Kw, &Vw, &Pw, &counters, &n_counters);
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(attn_pp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
@@ -996,7 +1008,7 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
     }
     const float qscale = 1.4426950408889634f / sqrtf((float)C);
     attn_pp_prep_kernel<<<dim3(NT128, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, NT128, qscale, 1.0f / sigma_spat,
-                                                                      Qw, Kw, Vw, Pw);
+                                                                      Qw, Kw, Vw, Pw, counters, n_counters);
     count_launches(1);
     return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, st);
 }

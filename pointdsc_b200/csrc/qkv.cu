@@ -21,7 +21,8 @@ namespace pdsc {
 
 using namespace sm100;
 
-void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw);   // attn_pp.cu
+void attn_pp_tile_pointers(void* ws, int B, int N, uint8_t** Qw, uint8_t** Kw, uint8_t** Vw, float** Pw, int** counters,
+                           int* n_counters);   // attn_pp.cu
 int attn_pp_tiles128(int N);
 
 constexpr int QK_GROUP = 256;         // threads per group: two per row (thread t and t + 128 take alternate 32-column chunks of row t)
@@ -32,7 +33,8 @@ constexpr uint32_t QK_PTS_FLOATS = 32 * 12 + 4;   // = PP_PTS_FLOATS (attn_pp.cu
 
 struct QkvParams {
     const float* y; const uint8_t* wpack; const float* bias; const float* src; const float* tgt;
-    uint8_t* Qw; uint8_t* Kw; uint8_t* Vw; float* Pw;
+    uint8_t* Qw; uint8_t* Kw; uint8_t* Vw; float* Pw; int* counters;
+    int n_counters;
     int B, N, NT128;
     float qscale, inv_sigma;
 };
@@ -88,6 +90,8 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
     const int N = p.N;
     const long long n_tiles = (long long)p.B * p.NT128;
     uint32_t mma_phase = 0;
+    if (blockIdx.x == 0 && blockIdx.y == 0)     // arrival counters of the attention kernel start at zero (no memset on the stream)
+        for (int i = threadIdx.x; i < p.n_counters; i += QK_THREADS) p.counters[i] = 0;
     for (long long tile = blockIdx.x + (long long)grp * gridDim.x; tile < n_tiles; tile += 2LL * gridDim.x) {
         const int b = (int)(tile / p.NT128), t = (int)(tile - (long long)b * p.NT128);
         const int n0 = t * 128;
@@ -215,7 +219,7 @@ int launch_qkv_pack(const float* y, const void* wpack, const float* bias, const 
     }
     QkvParams p;
     p.y = y; p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.src = src; p.tgt = tgt;
-    attn_pp_tile_pointers(ws, B, N, &p.Qw, &p.Kw, &p.Vw, &p.Pw);
+    attn_pp_tile_pointers(ws, B, N, &p.Qw, &p.Kw, &p.Vw, &p.Pw, &p.counters, &p.n_counters);
     p.B = B; p.N = N; p.NT128 = attn_pp_tiles128(N);
     p.qscale = 1.4426950408889634f / sqrtf((float)C);
     p.inv_sigma = 1.0f / sigma_spat;
