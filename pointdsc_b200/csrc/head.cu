@@ -3,17 +3,17 @@
 //   confidence = classification(corr_features)                        (:107-113, :171; Conv1d 128->32, ReLU, 32->32, ReLU, 32->1)
 // -- in ONE pass over the features.  As torch ops this was a norm reduction, a division, a clamp and three small library
 // GEMMs with their epilogues (~170 us for 16 x 5000 rows, each re-reading the 41 MB feature matrix); here a CTA stages a
-// 128-row tile in shared memory with coalesced loads, thread t walks row t once (sum of squares + the 128 -> 32 layer,
-// weights broadcast from shared memory), finishes the two small layers in registers, and the tile leaves normalised
-// with coalesced stores.  fp32 FMA throughout; the summation order differs from cuBLAS, i.e. results agree with the
-// torch path to fp32 rounding (tests: 1e-6 relative).
+// 128-row tile in shared memory with coalesced loads, threads t and t + 128 walk one half of row t each (sum of squares +
+// the 128 -> 32 layer, weights broadcast from shared memory; the halves meet in shared memory), thread t finishes the two
+// small layers in registers, and the tile leaves normalised with coalesced stores.  fp32 FMA throughout; the summation
+// order differs from cuBLAS, i.e. results agree with the torch path to fp32 rounding (tests: 1e-6 relative).
 #include "common.cuh"
 
 #include <math.h>
 
 namespace pdsc {
 
-constexpr int HD_THREADS = 128;
+constexpr int HD_THREADS = 256;          // two threads per row, 64 channels each
 constexpr int HD_C = 128, HD_H = 32;
 constexpr int HD_PITCH = HD_C + 4;          // floats: row t starts at bank 4t mod 32, so row-per-thread LDS.128 are conflict free
 
@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadPara
     float* b2 = b1 + HD_H;                             // [32]
     float* w3 = b2 + HD_H;                             // [32]
     float* den = w3 + HD_H;                            // [128] max(norm, eps) per row
+    float* part = den + 128;                           // [128][HD_H + 1] partial sums of the upper channel half
     const int tid = threadIdx.x;
     const long long row0 = (long long)blockIdx.x * 128;
     const int nrows = (int)min(128LL, p.rows - row0);
@@ -51,14 +52,15 @@ __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadPara
         if (tid < HD_H) { b1[tid] = p.b1[tid]; b2[tid] = p.b2[tid]; w3[tid] = p.w3[tid]; }
     }
     __syncthreads();
-    if (tid < nrows) {
-        const float* xr = xs + tid * HD_PITCH;
-        float h1[HD_H];
+    const int rt = tid & 127, half = tid >> 7;
+    float h1[HD_H];
+    float ss = 0.f;
+    if (rt < nrows) {
+        const float* xr = xs + rt * HD_PITCH;
 #pragma unroll
         for (int o = 0; o < HD_H; ++o) h1[o] = 0.f;
-        float ss = 0.f;
 #pragma unroll 2
-        for (int c4 = 0; c4 < HD_C / 4; ++c4) {
+        for (int c4 = half * (HD_C / 8); c4 < (half + 1) * (HD_C / 8); ++c4) {
             const float4 x4 = *reinterpret_cast<const float4*>(xr + c4 * 4);
             const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
@@ -75,8 +77,17 @@ __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadPara
                 }
             }
         }
+        if (half == 1) {
 #pragma unroll
-        for (int o = 0; o < HD_H; ++o) h1[o] = fmaxf(h1[o] + b1[o], 0.f);
+            for (int o = 0; o < HD_H; ++o) part[rt * (HD_H + 1) + o] = h1[o];
+            part[rt * (HD_H + 1) + HD_H] = ss;
+        }
+    }
+    __syncthreads();
+    if (half == 0 && rt < nrows) {
+#pragma unroll
+        for (int o = 0; o < HD_H; ++o) h1[o] = fmaxf((h1[o] + part[rt * (HD_H + 1) + o]) + b1[o], 0.f);
+        ss += part[rt * (HD_H + 1) + HD_H];
         float h2[HD_H];
 #pragma unroll
         for (int o = 0; o < HD_H; ++o) h2[o] = 0.f;
@@ -95,8 +106,8 @@ __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadPara
         float c = 0.f;
 #pragma unroll
         for (int o = 0; o < HD_H; ++o) c = fmaf(fmaxf(h2[o] + b2[o], 0.f), w3[o], c);
-        p.conf[row0 + tid] = c + p.b3[0];
-        den[tid] = fmaxf(sqrtf(ss), p.eps);            // F.normalize: x / max(||x||_2, eps)
+        p.conf[row0 + rt] = c + p.b3[0];
+        den[rt] = fmaxf(sqrtf(ss), p.eps);            // F.normalize: x / max(||x||_2, eps)
     }
     __syncthreads();
     {
@@ -120,7 +131,7 @@ int launch_feature_head(const float* feat, long long rows, int C, int H1, int H2
     HeadParams p;
     p.feat = feat; p.w1 = w1t; p.b1 = b1; p.w2 = w2t; p.b2 = b2; p.w3 = w3; p.b3 = b3;
     p.normed = normed; p.conf = conf; p.rows = rows; p.eps = eps;
-    const int smem = (int)sizeof(float) * (128 * HD_PITCH + HD_C * HD_H + HD_H * HD_H + 3 * HD_H + 128);
+    const int smem = (int)sizeof(float) * (128 * HD_PITCH + HD_C * HD_H + HD_H * HD_H + 3 * HD_H + 128 + 128 * (HD_H + 1));
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(feature_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
