@@ -295,9 +295,10 @@ __global__ void __launch_bounds__(KG_THREADS, 2) knn_dist_kernel(const float* __
 //   * the row is read from global memory ONCE, as ordered keys, into shared memory (rows of up to KS_SMEM_KEYS
 //     elements; longer rows are re-read from global memory, which L1/L2 serve); every thread keeps the minimum of
 //     the elements it staged;
-//   * fast path: the k-th smallest of the 128 thread minima is an upper bound of the k-th smallest element (the
-//     minima are k distinct elements below it), and only ~k * 1.2 elements of a row lie at or below it: they are
-//     compacted and rank-sorted by (key, index) directly -- exact, no histogram;
+//   * fast path: an upper bound of the k-th smallest element from the thread minima (every warp takes the
+//     ceil(k/4)-th smallest of its 32 minima, the largest of the four has at least k distinct elements at or below
+//     it); only ~k * 1.4 elements of a row lie at or below the bound: they are compacted and rank-sorted by
+//     (key, index) directly -- exact, no histogram;
 //   * slow path (more than KS_CAND elements at or below the bound: heavy ties): 4-pass radix select on the keys.  Distances 2 - 2 cos sit in a narrow band, so the first passes put nearly every
 //     element into one bin: votes are aggregated per warp (__match_any_sync) before the shared-memory atomic;
 //   * one ordered pass: every thread owns a contiguous segment of the row, a block scan of the per-thread counts
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(KS_THREADS) knn_select_kernel(const float* __r
     __shared__ unsigned int sh_prefix, sh_want;
     __shared__ unsigned int cand_key[KS_CAND];
     __shared__ int cand_idx[KS_CAND];
-    __shared__ __align__(16) unsigned int tmin[KS_THREADS];
+    __shared__ unsigned int warp_bound[KS_THREADS / 32];
     __shared__ unsigned int sh_bound;
     __shared__ int n_cand;
     __shared__ int warp_less[KS_THREADS / 32], warp_eq[KS_THREADS / 32];
@@ -334,22 +335,24 @@ __global__ void __launch_bounds__(KS_THREADS) knn_select_kernel(const float* __r
         if (SMEM) keys[j] = key;
         my_min = min(my_min, key);
     }
-    tmin[tid] = my_min;
     if (tid == 0) { sh_prefix = 0u; sh_want = (unsigned)k; n_cand = 0; }
-    __syncthreads();
     {
-        // rank of this thread's minimum among the 128 minima, ties broken by thread index (so ranks are distinct)
+        // every warp finds the q-th smallest of its 32 minima (rank by counting over shuffles, ties broken by lane),
+        // q = ceil(k / warps): the largest of the four has at least 4 q >= k elements at or below it
         int rank = 0;
 #pragma unroll 8
-        for (int o4 = 0; o4 < KS_THREADS / 4; ++o4) {
-            const uint4 m = *reinterpret_cast<const uint4*>(&tmin[o4 * 4]);
-            const int o = o4 * 4;
-            rank += (m.x < my_min || (m.x == my_min && o < tid)) ? 1 : 0;
-            rank += (m.y < my_min || (m.y == my_min && o + 1 < tid)) ? 1 : 0;
-            rank += (m.z < my_min || (m.z == my_min && o + 2 < tid)) ? 1 : 0;
-            rank += (m.w < my_min || (m.w == my_min && o + 3 < tid)) ? 1 : 0;
+        for (int o = 0; o < 32; ++o) {
+            const unsigned m = __shfl_sync(0xffffffffu, my_min, o);
+            rank += (m < my_min || (m == my_min && o < lane)) ? 1 : 0;
         }
-        if (rank == k - 1) sh_bound = my_min;        // k elements (thread minima) are <= this key
+        constexpr int NW = KS_THREADS / 32;
+        if (rank == (k + NW - 1) / NW - 1) warp_bound[warp] = my_min;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned bmax = warp_bound[0];
+        for (int w = 1; w < KS_THREADS / 32; ++w) bmax = max(bmax, warp_bound[w]);
+        sh_bound = bmax;
     }
     __syncthreads();
     {
