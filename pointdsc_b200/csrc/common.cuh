@@ -177,6 +177,16 @@ __device__ inline void write_transform(float* T, const double R[9], const float 
     T[12] = 0.f; T[13] = 0.f; T[14] = 0.f; T[15] = 1.f;
 }
 
+// Squared-distance threshold equivalent to comparing the fp32 norm with R: sqrtf is monotone and correctly rounded, so
+// sqrtf(d2) >= R  <=>  d2 >= T2 (and sqrtf(d2) < R  <=>  d2 < T2) with T2 the smallest fp32 whose square root reaches R.
+inline float squared_threshold(float R) {
+    if (!(R > 0.f)) return 0.f;                       // every distance is >= R
+    float T2 = R * R;
+    while (T2 > 0.f && sqrtf(T2) >= R) T2 = nextafterf(T2, 0.f);
+    while (sqrtf(T2) < R) T2 = nextafterf(T2, INFINITY);
+    return T2;
+}
+
 // ---- launchers implemented in the .cu files -------------------------------------------------
 int launch_score_hypotheses(const float* seed_trans, const float* src, const float* tgt, int B, int N, int S,
                             float thr, int32_t* inlier_count, int64_t* best_idx, float* final_trans,

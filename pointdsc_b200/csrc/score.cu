@@ -15,11 +15,21 @@ __device__ __forceinline__ bool is_inlier(const float* T, float sx, float sy, fl
     float pz = fmaf(T[10], sz, fmaf(T[9], sy, T[8] * sx)) + T[11];
     return dist3(px, py, pz, tx, ty, tz) < thr;
 }
+// Same decision without the square root: thr2 = squared_threshold(thr) (common.cuh), d2 rounded like dist3's argument.
+__device__ __forceinline__ bool is_inlier_sq(const float* T, float sx, float sy, float sz, float tx, float ty, float tz,
+                                             float thr2) {
+    float px = fmaf(T[2], sz, fmaf(T[1], sy, T[0] * sx)) + T[3];
+    float py = fmaf(T[6], sz, fmaf(T[5], sy, T[4] * sx)) + T[7];
+    float pz = fmaf(T[10], sz, fmaf(T[9], sy, T[8] * sx)) + T[11];
+    const float dx = px - tx, dy = py - ty, dz = pz - tz;
+    const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+    return d2 < thr2;
+}
 
 __global__ void __launch_bounds__(SC_THREADS) score_count_kernel(const float* __restrict__ seed_trans,
                                                                  const float* __restrict__ src,
                                                                  const float* __restrict__ tgt, int N, int S,
-                                                                 float thr, int32_t* __restrict__ inlier_count) {
+                                                                 float thr2, int32_t* __restrict__ inlier_count) {
     __shared__ float sp[SC_POINTS * 6];
     const int b = blockIdx.z;
     const int n0 = blockIdx.y * SC_POINTS;
@@ -45,7 +55,7 @@ __global__ void __launch_bounds__(SC_THREADS) score_count_kernel(const float* __
     for (int n = 0; n < np; ++n) {
         const float* a = sp + n * 3;
         const float* c = sp + SC_POINTS * 3 + n * 3;
-        cnt += is_inlier(T, a[0], a[1], a[2], c[0], c[1], c[2], thr) ? 1 : 0;
+        cnt += is_inlier_sq(T, a[0], a[1], a[2], c[0], c[1], c[2], thr2) ? 1 : 0;
     }
     atomicAdd(inlier_count + (size_t)b * S + s, cnt);
 }
@@ -103,7 +113,7 @@ int launch_score_hypotheses(const float* seed_trans, const float* src, const flo
                             float* final_labels, cudaStream_t st) {
     cudaMemsetAsync(inlier_count, 0, sizeof(int32_t) * (size_t)B * S, st);
     dim3 grid((S + SC_THREADS - 1) / SC_THREADS, (N + SC_POINTS - 1) / SC_POINTS, B);
-    score_count_kernel<<<grid, SC_THREADS, 0, st>>>(seed_trans, src, tgt, N, S, thr, inlier_count);
+    score_count_kernel<<<grid, SC_THREADS, 0, st>>>(seed_trans, src, tgt, N, S, squared_threshold(thr), inlier_count);
     score_select_kernel<<<B, 256, 0, st>>>(seed_trans, src, tgt, N, S, thr, inlier_count, best_idx, final_trans,
                                            final_labels);
     count_launches(2);

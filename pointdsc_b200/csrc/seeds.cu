@@ -181,13 +181,7 @@ int launch_pick_seeds(const float* src, const float* scores, int B, int N, float
     jchunk = (jchunk + NMS_TILE - 1) / NMS_TILE * NMS_TILE;
     jsplit = (N + jchunk - 1) / jchunk;
     // squared-distance threshold equivalent to the reference's `norm >= R` (sqrtf is monotone and correctly rounded)
-    float T2 = R * R;
-    if (R <= 0.f) {
-        T2 = 0.f;                                     // every distance is >= R
-    } else {
-        while (T2 > 0.f && sqrtf(T2) >= R) T2 = nextafterf(T2, 0.f);
-        while (sqrtf(T2) < R) T2 = nextafterf(T2, INFINITY);
-    }
+    const float T2 = squared_threshold(R);
     nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, T2, jchunk, suppressed);
     const int p2 = next_pow2(N);
     unsigned long long* gbuf = nullptr;
