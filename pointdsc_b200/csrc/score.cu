@@ -26,36 +26,56 @@ __device__ __forceinline__ bool is_inlier_sq(const float* T, float sx, float sy,
     return d2 < thr2;
 }
 
+// Two correspondences per packed f32x2 instruction (each lane rounded like the scalar operation of is_inlier_sq: the
+// counts are identical).  The two sums of the squared distance stay scalar: ptxas contracts mul.rn.f32x2 + add.rn.f32x2.
 __global__ void __launch_bounds__(SC_THREADS) score_count_kernel(const float* __restrict__ seed_trans,
                                                                  const float* __restrict__ src,
                                                                  const float* __restrict__ tgt, int N, int S,
                                                                  float thr2, int32_t* __restrict__ inlier_count) {
-    __shared__ float sp[SC_POINTS * 6];
+    // per pair of points: (sx0, sx1, sy0, sy1), (sz0, sz1, -tx0, -tx1), (-ty0, -ty1, -tz0, -tz1)
+    __shared__ float4 sp[SC_POINTS / 2 * 3];
     const int b = blockIdx.z;
     const int n0 = blockIdx.y * SC_POINTS;
     const int np = min(SC_POINTS, N - n0);
+    const int np2 = (np + 1) >> 1;
     const float* sb = src + ((size_t)b * N + n0) * 3;
     const float* tb = tgt + ((size_t)b * N + n0) * 3;
-    for (int i = threadIdx.x; i < np * 3; i += SC_THREADS) {
-        sp[i] = sb[i];
-        sp[SC_POINTS * 3 + i] = tb[i];
+    for (int i = threadIdx.x; i < np2; i += SC_THREADS) {
+        const int n = 2 * i;
+        const bool two = n + 1 < np;
+        // an odd tail is padded with a target infinitely far away: never an inlier
+        const float sx1 = two ? sb[n * 3 + 3] : 0.f, sy1 = two ? sb[n * 3 + 4] : 0.f, sz1 = two ? sb[n * 3 + 5] : 0.f;
+        const float tx1 = two ? tb[n * 3 + 3] : INFINITY, ty1 = two ? tb[n * 3 + 4] : INFINITY, tz1 = two ? tb[n * 3 + 5] : INFINITY;
+        sp[i * 3 + 0] = make_float4(sb[n * 3], sx1, sb[n * 3 + 1], sy1);
+        sp[i * 3 + 1] = make_float4(sb[n * 3 + 2], sz1, -tb[n * 3], -tx1);
+        sp[i * 3 + 2] = make_float4(-tb[n * 3 + 1], -ty1, -tb[n * 3 + 2], -tz1);
     }
     __syncthreads();
     const int s = blockIdx.x * SC_THREADS + threadIdx.x;
     if (s >= S) return;
-    float T[12];
+    float2 T[12];
     const float4* tp = reinterpret_cast<const float4*>(seed_trans + ((size_t)b * S + s) * 16);
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-        float4 row = tp[r];
-        T[r * 4 + 0] = row.x; T[r * 4 + 1] = row.y; T[r * 4 + 2] = row.z; T[r * 4 + 3] = row.w;
+        const float4 row = tp[r];
+        T[r * 4 + 0] = make_float2(row.x, row.x); T[r * 4 + 1] = make_float2(row.y, row.y);
+        T[r * 4 + 2] = make_float2(row.z, row.z); T[r * 4 + 3] = make_float2(row.w, row.w);
     }
     int cnt = 0;
 #pragma unroll 4
-    for (int n = 0; n < np; ++n) {
-        const float* a = sp + n * 3;
-        const float* c = sp + SC_POINTS * 3 + n * 3;
-        cnt += is_inlier_sq(T, a[0], a[1], a[2], c[0], c[1], c[2], thr2) ? 1 : 0;
+    for (int i = 0; i < np2; ++i) {
+        const float4 a = sp[i * 3], c = sp[i * 3 + 1], e = sp[i * 3 + 2];
+        const float2 sx = make_float2(a.x, a.y), sy = make_float2(a.z, a.w), sz = make_float2(c.x, c.y);
+        // p = fma(T2, sz, fma(T1, sy, T0 * sx)) + T3, exactly as is_inlier_sq
+        const float2 px = __fadd2_rn(__ffma2_rn(T[2], sz, __ffma2_rn(T[1], sy, __fmul2_rn(T[0], sx))), T[3]);
+        const float2 py = __fadd2_rn(__ffma2_rn(T[6], sz, __ffma2_rn(T[5], sy, __fmul2_rn(T[4], sx))), T[7]);
+        const float2 pz = __fadd2_rn(__ffma2_rn(T[10], sz, __ffma2_rn(T[9], sy, __fmul2_rn(T[8], sx))), T[11]);
+        const float2 dx = __fadd2_rn(px, make_float2(c.z, c.w));
+        const float2 dy = __fadd2_rn(py, make_float2(e.x, e.y));
+        const float2 dz = __fadd2_rn(pz, make_float2(e.z, e.w));
+        const float2 qx = __fmul2_rn(dx, dx), qy = __fmul2_rn(dy, dy), qz = __fmul2_rn(dz, dz);
+        const float d0 = __fadd_rn(__fadd_rn(qx.x, qy.x), qz.x), d1 = __fadd_rn(__fadd_rn(qx.y, qy.y), qz.y);
+        cnt += (d0 < thr2 ? 1 : 0) + (d1 < thr2 ? 1 : 0);
     }
     atomicAdd(inlier_count + (size_t)b * S + s, cnt);
 }
