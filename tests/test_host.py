@@ -91,6 +91,8 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     assert lib.pdsc_icp_refine(1, 1, 1, 1, 10, -0.1, 30, 1e-6, 1e-6, None, None, None, 1, 0, None) == 1
     assert b"icp_refine" in lib.pdsc_last_error()
     assert lib.pdsc_pick_seeds(None, None, 1, 10, 0.1, 1, None, None, None, None, 0, None) == 1
+    assert lib.pdsc_feature_head(None, 10, 128, 32, 32, None, None, None, None, None, None, 1e-12, None, None, None) == 1
+    assert b"feature_head" in lib.pdsc_last_error()
 
 
 def test_front_end_and_icp_refuse_cpu_tensors():
