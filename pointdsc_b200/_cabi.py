@@ -14,8 +14,11 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
+# the same sources built with -DPDSC_TUNING: the only build that reads the PDSC_* debug / tuning environment variables
+# (tests and scripts/ select it with use_tuning_library(); the product path never loads it)
+TUNING_LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200_tuning.so")
 
-ATTN_FP32, ATTN_SPLIT16, ATTN_FP16 = 0, 1, 2
+ATTN_FP32, ATTN_SPLIT16, ATTN_FP16, ATTN_SPLIT16X3 = 0, 1, 2, 3
 OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
 OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
 OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE, OP_NN_MATCH_F64, OP_ICP_REFINE = 8, 9, 10, 11
@@ -68,25 +71,46 @@ SIGNATURES = {
                                      c_void_p, c_size_t, c_void_p]),
 }
 
-_lib = None
+_libs = {}         # path -> loaded library
+_active = LIB_PATH
 launch_count = 0   # kernels-launching C-ABI calls made through this binding (bench.py reports it)
 
 
 def load():
     """Loads the shared library (no CUDA context needed) and declares every signature."""
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
+    lib = _libs.get(_active)
+    if lib is None:
+        if not os.path.exists(_active):
             raise RuntimeError(
-                f"{LIB_PATH} is missing: build it with `python -m pointdsc_b200.build` "
+                f"{_active} is missing: build it with `python -m pointdsc_b200.build` "
                 "(there is no CPU or PyTorch fallback for the CUDA path)")
-        lib = ctypes.CDLL(LIB_PATH)
+        lib = ctypes.CDLL(_active)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
-        _lib = lib
-    return _lib
+        _libs[_active] = lib
+    return lib
+
+
+class use_tuning_library:
+    """Context manager for tests / scripts: calls made inside go to libpointdsc_b200_tuning.so, which reads the PDSC_*
+    knobs from the environment.  The product library ignores them."""
+
+    def __enter__(self):
+        global _active
+        self._prev = _active
+        _active = TUNING_LIB_PATH
+        return load()
+
+    def __exit__(self, *exc):
+        global _active
+        _active = self._prev
+        return False
+
+
+def is_tuning_library():
+    return _active == TUNING_LIB_PATH
 
 
 def _check(rc, what):

@@ -42,6 +42,17 @@ int num_sms() {
     return cached > 0 ? cached : 148;
 }
 
+#ifdef PDSC_TUNING
+int tuning_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && e[0]) ? atoi(e) : dflt;
+}
+const char* tuning_str(const char* name) {
+    const char* e = getenv(name);
+    return (e && e[0]) ? e : nullptr;
+}
+#endif
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 }  // namespace pdsc
@@ -73,8 +84,7 @@ size_t pdsc_workspace_bytes(int op, int B, int N, int C, int S, int k, int mode)
     switch (op) {
         case PDSC_OP_NONLOCAL_ATTN: {
             if (mode == PDSC_ATTN_FP32) return 0;
-            const size_t a = attn_workspace(B, N, C, mode), b = attn_pp_workspace(B, N);
-            return a > b ? a : b;
+            return attn_pp_workspace(B, N);
         }
         case PDSC_OP_PICK_SEEDS: return pick_seeds_workspace(B, N);
         case PDSC_OP_HYBRID_SEARCH: return frontend_search_workspace(N);
@@ -100,13 +110,8 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
     PDSC_REQUIRE(sigma_spat > 0.f, "nonlocal_attn: sigma_spat must be positive");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (mode == PDSC_ATTN_FP32) return launch_attn_fp32(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, st);
-    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16) {
-        static int impl = -1;                       // PDSC_ATTN_IMPL=tc selects the previous single-tile kernel
-        if (impl < 0) { const char* e = getenv("PDSC_ATTN_IMPL"); impl = (e && e[0] == 't') ? 1 : 0; }
-        if (impl == 0)
-            return launch_attn_pp(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
-        return launch_attn_tc(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
-    }
+    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16X3)
+        return launch_attn_pp(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
     set_error("nonlocal_attn: unknown precision mode %d", mode);
     return PDSC_ERR_ARG;
 }
@@ -125,7 +130,8 @@ int pdsc_nonlocal_attn_packed(float* out, int64_t ld_out, int B, int N, int C, i
     PDSC_REQUIRE(out && ws, "nonlocal_attn_packed: null pointer");
     PDSC_REQUIRE(B > 0 && N > 0, "nonlocal_attn_packed: bad shape B=%d N=%d", B, N);
     PDSC_REQUIRE(ld_out >= C && ld_out % 4 == 0 && aligned16(out), "nonlocal_attn_packed: bad output stride/alignment");
-    PDSC_REQUIRE(mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16, "nonlocal_attn_packed: mode must be SPLIT16 or FP16");
+    PDSC_REQUIRE(mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16X3,
+                 "nonlocal_attn_packed: mode must be SPLIT16, SPLIT16X3 or FP16");
     return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 

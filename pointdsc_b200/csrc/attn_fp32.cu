@@ -180,11 +180,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) attn_fp32_kernel(
 int launch_attn_fp32(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
                      float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, cudaStream_t st) {
     if (C != AF_C) { set_error("nonlocal_attn: C=%d unsupported (kernels are built for C=%d)", C, AF_C); return PDSC_ERR_ARG; }
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(attn_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnFp32Smem));
-        attr_set = true;
-    }
+    opt_in_smem<attn_fp32_kernel>((int)sizeof(AttnFp32Smem));
     const float scale = 1.0f / sqrtf((float)C);
     dim3 grid((N + AF_BM - 1) / AF_BM, B);
     attn_fp32_kernel<<<grid, AF_THREADS, sizeof(AttnFp32Smem), st>>>(q, k, v, ld, src, tgt, out, ld_out, N,

@@ -6,9 +6,15 @@
 //                                  (never stored), online softmax with a lazily raised reference max
 //   msg = W V                      tcgen05.mma with P read from TMEM (aliasing S) and V^T from smem
 //
-// Precision (PDSC_ATTN_SPLIT16): every fp32 operand x is split into fp16 hi + fp16 lo (22 mantissa
-// bits) and each contraction is issued as hi*hi + hi*lo + lo*hi with fp32 accumulation.
-// PDSC_ATTN_FP16 issues only hi*hi.
+// Precision: every fp32 operand x is split into fp16 hi + fp16 lo (22 mantissa bits), fp32 accumulation.
+//   PDSC_ATTN_SPLIT16X3  both contractions as hi*hi + hi*lo + lo*hi (3 MMAs per k-step).
+//   PDSC_ATTN_SPLIT16    (default) Q K^T with all three terms; P V as P_hi V_hi + P_hi V_lo.  The reference maximum of the
+//                        online softmax is kept an INTEGER (log2 units), so the weight of every key with compat = 0 -- the
+//                        great majority: logit exactly 0, weight exp2(-m) -- is a power of two and exact in fp16; the
+//                        remaining weights carry independent fp16 rounding errors, and because the row sum is taken over
+//                        the SAME rounded weights they only perturb a softmax that is then re-normalised (no P_lo term
+//                        needed: as accurate as X3 in scripts/precision_study.py and in the parity reports).
+//   PDSC_ATTN_FP16       hi*hi only.
 //
 // One CTA works on 256 query rows of one pair as two 128-row sub-tiles X = A, B that alternate on
 // the tensor pipe (while the CUDA cores do the softmax of one, the tensor cores do the MMAs of the
@@ -47,7 +53,11 @@ constexpr uint32_t PP_VHALF_BYTES = 16384;
 // that the two half-warps (which read pairs i and 16 + i in one LDS.128) hit different banks
 constexpr uint32_t PP_PTS_FLOATS = (PP_BN / 2) * 12 + 4;
 constexpr uint32_t PP_PTS_BYTES = PP_PTS_FLOATS * 4;
-constexpr float PP_RESCALE_LOG2 = 8.0f;      // lazy rescale threshold (log2 units)
+// Lazy reference maximum (log2 units, always an integer): raised when a row maximum would put P above 2^PP_RESCALE_LOG2,
+// and then set so that the maximum sits at 2^PP_TOP_LOG2.  fp16 holds P up to 2^15, so weights down to 2^-(14+6) of the
+// row maximum stay normal numbers and down to 2^-30 subnormal (they were flushed 2^6 earlier with the maximum at 2^0).
+constexpr float PP_RESCALE_LOG2 = 14.0f;
+constexpr float PP_TOP_LOG2 = 6.0f;
 constexpr uint32_t PT_S = 0, PT_O = 128, PT_Q = 384;
 constexpr int PP_SOFT_WARPS = 16;
 constexpr int PP_DEFAULT_CLUSTER = 1;                  // CTAs per cluster unless PDSC_ATTN_CLUSTER says otherwise
@@ -251,15 +261,14 @@ __device__ __forceinline__ void pp_pv_run(uint64_t v_desc, uint32_t acc_first) {
                  : "memory");
 }
 
-// S_X[128 x 64 keys] = Q K^T.  terms = 3: Qhi Khi + Qhi Klo + Qlo Khi; 1: Qhi Khi.
+// S_X[128 x 64 keys] = Q K^T.  terms: bit 0 = Qhi Khi, bit 1 = Qhi Klo, bit 2 = Qlo Khi (0 = no MMAs: timing experiments).
+constexpr int PP_QK_HH = 1, PP_QK_HL = 2, PP_QK_LH = 4;
 template <int X>
 __device__ __forceinline__ void pp_issue_qk(uint64_t qlo_desc, uint64_t k_desc, int terms) {
-    if (terms <= 0) return;
+    if (!(terms & PP_QK_HH)) return;
     pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(k_desc, 0u);
-    if (terms > 1) {
-        pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), 1u);
-        pp_qk_run_ss<PT_S + 64u * X>(qlo_desc, k_desc);
-    }
+    if (terms & PP_QK_HL) pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), 1u);
+    if (terms & PP_QK_LH) pp_qk_run_ss<PT_S + 64u * X>(qlo_desc, k_desc);
 }
 // O_X[128 x 128 ch] (+)= P[128 x 64 keys] V.  terms = 3: Phi Vhi + Phi Vlo + Plo Vhi; 2: Phi Vhi + Phi Vlo; 1: Phi Vhi.
 template <int X>
@@ -364,7 +373,8 @@ __device__ __forceinline__ float4 pp_ldcg4(const float* p) {
 // 256-row blocks; each loads HALF of every K / V^T tile and multicasts it to both (cp.async.bulk .multicast::cluster),
 // which halves the L2 -> SM traffic; a stage is released by both MMA issuers (multicast tcgen05.commit).
 // DBG: instantiation with the timing-experiment knobs (PDSC_ATTN_DBG) and the timeline trace compiled in.
-template <int CL, bool DBG, bool CHAIN = false>
+// PV3: the P_lo V_hi term is issued (PDSC_ATTN_SPLIT16X3), so the softmax threads also store the fp16 remainder of P.
+template <int CL, bool DBG, bool CHAIN = false, bool PV3 = false>
 __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p) {
     constexpr int NP = 16;                   // key pairs per thread per tile (32 keys)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -528,7 +538,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const uint32_t q_x = tmem + lane_addr + PT_Q + 64u * x;
         const int kp0 = half * NP;                    // first key pair of this thread inside a tile
         const int dbg = DBG ? p.dbg : 0;
-        const bool pv3 = p.pv_terms > 2;
+        constexpr bool pv3 = PV3;
         const int N = p.N;
         long long pos = lo;
         PpSeg s;
@@ -612,11 +622,11 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     }
                 }
                 emax = fmaxf(emax, __shfl_xor_sync(0xffffffffu, emax, 16));   // the other half of the row
-                // Lazy reference max: raised only when the row maximum exceeds it by more than 2^8; on
-                // the first tile it is also lowered for rows whose logits are all far below zero.
-                const bool need = (emax > PP_RESCALE_LOG2) || (t == 0 && emax < -PP_RESCALE_LOG2 && emax > -INFINITY);
+                // Lazy reference max (an integer, see PP_RESCALE_LOG2): raised only when the row maximum would exceed
+                // 2^14; on the first tile it is also lowered for rows whose logits are all below zero.
+                const bool need = (emax > PP_RESCALE_LOG2) || (t == 0 && emax < -2.0f && emax > -INFINITY);
                 if (__any_sync(0xffffffffu, need)) {
-                    const float shift = need ? emax : 0.f;
+                    const float shift = need ? rintf(emax) - PP_TOP_LOG2 : 0.f;
                     const float f = fast_exp2(-shift);
                     m += shift;
                     l *= f;
@@ -816,20 +826,23 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
 }
 
 // ------------------------------------------------------------------------------------------------
-// PDSC_ATTN_CLUSTER (read per call; tuning knob): CTAs per cluster, 1 or 2.
-static int pp_cluster() {
-    const char* e = getenv("PDSC_ATTN_CLUSTER");
-    const int c = e ? atoi(e) : PP_DEFAULT_CLUSTER;
-    return c == 2 ? 2 : 1;
-}
+// Tuning knobs below are read only by the -DPDSC_TUNING build (common.cuh); the shipped library uses the defaults.
+// PDSC_ATTN_CLUSTER: CTAs per cluster, 1 or 2.
+static int pp_cluster() { return tuning_int("PDSC_ATTN_CLUSTER", PP_DEFAULT_CLUSTER) == 2 ? 2 : 1; }
 
 static int pp_smem_bytes() { return (int)sizeof(PpSmem) + 1024; }
 
 // clusters of 2 that can be resident at once (one CTA per SM; both CTAs of a cluster sit in one GPC)
+#ifndef PDSC_TUNING
+static int pp_max_clusters() { return 0; }      // the shipped library never launches the cluster instantiation
+#else
 static int pp_max_clusters() {
-    static int cached = -1;
-    if (cached >= 0) return cached;
-    cudaFuncSetAttribute(attn_pp_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, pp_smem_bytes());
+    static thread_local int cached = -1, cached_dev = -1;       // per device, like num_sms()
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cached >= 0 && dev == cached_dev) return cached;
+    cached_dev = dev;
+    opt_in_smem<attn_pp_kernel<2, false>>(pp_smem_bytes());
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * num_sms()); cfg.blockDim = dim3(PP_THREADS); cfg.dynamicSmemBytes = pp_smem_bytes();
     cudaLaunchAttribute at[1];
@@ -841,14 +854,13 @@ static int pp_max_clusters() {
     cached = n;
     return n;
 }
+#endif
 
 // number of work ranges (= CTAs without clusters, = clusters with them)
 static int pp_grid(int B, int NU, int NT, int CL) {
     const long long total = (long long)B * NU * NT;
-    // PDSC_ATTN_GRID (read per call; a test/tuning knob): unset = one CTA per SM (stream-K),
-    // 0 = one range per work unit (no partials), n = n ranges
-    const char* e = getenv("PDSC_ATTN_GRID");
-    const int knob = e ? atoi(e) : -1;
+    // PDSC_ATTN_GRID (tuning build): unset = one CTA per SM (stream-K), 0 = one range per work unit (no partials), n = n ranges
+    const int knob = tuning_int("PDSC_ATTN_GRID", -1);
     long long g = knob < 0 ? (CL == 1 ? num_sms() : pp_max_clusters()) : (knob == 0 ? (long long)B * NU : knob);
     if (g > total) g = total;
     if (g < 1) g = 1;
@@ -863,7 +875,7 @@ static PpLayout pp_layout(int B, int N) {
     const int NRBp = (NRB + 1) & ~1;
     const size_t t128 = (size_t)B * 2 * NRBp;
     // partial slots for the larger of the two launch shapes, so the layout does not depend on the cluster knob
-    const size_t G = (size_t)std::max(pp_grid(B, NRB, NT, 1), 2 * pp_grid(B, NRBp / 2, NT, 2));
+    const size_t G = (size_t)std::max(pp_grid(B, NRB, NT, 1), kTuningBuild ? 2 * pp_grid(B, NRBp / 2, NT, 2) : 0);
     PpLayout L;
     size_t off = 0;
     L.q = off; off += t128 * PP_QTILE_BYTES;
@@ -872,7 +884,7 @@ static PpLayout pp_layout(int B, int N) {
     L.pts = off; off += align_up(t128 * 2 * PP_PTS_BYTES, 1024);
     L.part_o = off; off += G * 2 * 2 * PP_SUB * PP_C * sizeof(float);
     L.part_ml = off; off += G * 2 * 2 * PP_SUB * 2 * sizeof(float);
-    L.chain_o = off; off += (NT > 100 || getenv("PDSC_ATTN_CHAIN") ? (size_t)PP_CHAIN_SLOTS : 0) * G * 2 * PP_SUB * PP_C * sizeof(float);
+    L.chain_o = off; off += (NT > 100 || tuning_int("PDSC_ATTN_CHAIN", -1) >= 0 ? (size_t)PP_CHAIN_SLOTS : 0) * G * 2 * PP_SUB * PP_C * sizeof(float);
     L.chain_m = off; off += (size_t)PP_CHAIN_SLOTS * G * 2 * PP_SUB * sizeof(float);
     L.counters = off; off += align_up((size_t)B * NRBp * 2 * sizeof(int), 1024);
     L.n_counters = (size_t)B * NRBp * 2;
@@ -915,11 +927,10 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.chain_o = reinterpret_cast<float*>(base + L.chain_o);
     p.chain_m = reinterpret_cast<float*>(base + L.chain_m);
     {   // chain limit (see the work-decomposition comment): on for blocks longer than 100 key tiles (N > 6400);
-        // PDSC_ATTN_CHAIN (read per call; a test/tuning knob) overrides the chain length, 0 = no limit.  At most
-        // PP_CHAIN_SLOTS finished chains per segment: very long blocks get proportionally longer chains.
-        const char* e = getenv("PDSC_ATTN_CHAIN");
-        p.chain = e ? atoi(e) : (NT > 100 ? 48 : 0);
-        if (p.chain < 0) p.chain = 0;
+        // PDSC_ATTN_CHAIN (tuning build) overrides the chain length, 0 = no limit.  At most PP_CHAIN_SLOTS finished
+        // chains per segment: very long blocks get proportionally longer chains.
+        const int knob = tuning_int("PDSC_ATTN_CHAIN", -1);
+        p.chain = knob >= 0 ? knob : (NT > 100 ? 48 : 0);
         if (p.chain > 0 && (NT - 1) / p.chain > PP_CHAIN_SLOTS) p.chain = (NT - 1) / PP_CHAIN_SLOTS + 1;
     }
     const int CL = pp_cluster();
@@ -927,46 +938,57 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.N = N; p.NT = NT; p.NRBp = NRBp;
     p.NU = CL == 1 ? NRB : NRBp / 2;
     p.total_steps = (long long)B * p.NU * NT;
-    // PDSC_ATTN_SPLIT16: all three hi/lo terms for both contractions.  PDSC_ATTN_PV_TERMS=2 (tuning knob) drops
-    // the P_lo V_hi term and takes the row sum over the rounded P_hi: ~2e-4 relative message error.
-    // PDSC_ATTN_FP16: hi*hi only.
-    p.qk_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
-    p.pv_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : 1;
-    if (mode == PDSC_ATTN_SPLIT16) { const char* e = getenv("PDSC_ATTN_PV_TERMS"); if (e && atoi(e) >= 1 && atoi(e) <= 3) p.pv_terms = atoi(e); }
-    // PDSC_ATTN_DBG (read per call): selects the debug instantiation; bits 1 / 2 / 4 switch off the compat arithmetic,
+    // hi/lo product terms per contraction (see the precision note at the top of the file)
+    const bool split = mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_SPLIT16X3;
+    p.qk_terms = split ? (PP_QK_HH | PP_QK_HL | PP_QK_LH) : PP_QK_HH;
+    p.pv_terms = mode == PDSC_ATTN_SPLIT16X3 ? 3 : (mode == PDSC_ATTN_SPLIT16 ? 2 : 1);
+    if (split) {   // PDSC_ATTN_QK_TERMS (bit mask) / PDSC_ATTN_PV_TERMS (1..3): tuning build only
+        const int qk = tuning_int("PDSC_ATTN_QK_TERMS", -1), pv = tuning_int("PDSC_ATTN_PV_TERMS", -1);
+        if (qk >= 1 && qk <= 7 && (qk & 1)) p.qk_terms = qk;
+        if (pv >= 1 && pv <= 3) p.pv_terms = pv;
+    }
+    // PDSC_ATTN_DBG (tuning build): selects the debug instantiation; bits 1 / 2 / 4 switch off the compat arithmetic,
     // the exp, the MMAs (timing experiments only, results are then wrong); 8 sets no knob
-    const char* dbg_env = getenv("PDSC_ATTN_DBG");
-    const int dbg = dbg_env ? atoi(dbg_env) : 0;
+    const int dbg = tuning_int("PDSC_ATTN_DBG", 0);
     p.dbg = dbg;
     if (dbg & 4) p.qk_terms = p.pv_terms = 0;       // no MMAs
     const int smem_bytes = pp_smem_bytes();
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(attn_pp_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        cudaFuncSetAttribute(attn_pp_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        cudaFuncSetAttribute(attn_pp_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        cudaFuncSetAttribute(attn_pp_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        attr_set = true;
-    }
+    opt_in_smem<attn_pp_kernel<1, false>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<1, false, true>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<1, false, false, true>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<1, false, true, true>>(smem_bytes);
+    const bool pv3 = p.pv_terms > 2;
     const int G = pp_grid(B, p.NU, NT, CL);
     p.trace = nullptr;
-    const char* trace_path = getenv("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
+#ifdef PDSC_TUNING
+    opt_in_smem<attn_pp_kernel<2, false>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<2, false, false, true>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<1, true>>(smem_bytes);
+    opt_in_smem<attn_pp_kernel<1, true, false, true>>(smem_bytes);
+    const char* trace_path = tuning_str("PDSC_ATTN_TRACE");     // debugging aid: timeline of CTA 0, written as text
     if (trace_path) { cudaMalloc(&p.trace, sizeof(long long) * 16 * 256); cudaMemset(p.trace, 0, sizeof(long long) * 16 * 256); }
     if (CL == 1 && (dbg || trace_path)) {
-        attn_pp_kernel<1, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
-    } else if (CL == 1 && p.chain > 0) {
-        attn_pp_kernel<1, false, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
-    } else if (CL == 1) {
-        attn_pp_kernel<1, false><<<G, PP_THREADS, smem_bytes, st>>>(p);
-    } else {
+        if (pv3) attn_pp_kernel<1, true, false, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+        else attn_pp_kernel<1, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+    } else if (CL == 2) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(2 * G); cfg.blockDim = dim3(PP_THREADS); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        cudaLaunchKernelEx(&cfg, attn_pp_kernel<2, false>, p);
+        if (pv3) cudaLaunchKernelEx(&cfg, attn_pp_kernel<2, false, false, true>, p);
+        else cudaLaunchKernelEx(&cfg, attn_pp_kernel<2, false>, p);
+    } else
+#endif
+    if (p.chain > 0) {
+        if (pv3) attn_pp_kernel<1, false, true, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+        else attn_pp_kernel<1, false, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+    } else {
+        if (pv3) attn_pp_kernel<1, false, false, true><<<G, PP_THREADS, smem_bytes, st>>>(p);
+        else attn_pp_kernel<1, false><<<G, PP_THREADS, smem_bytes, st>>>(p);
     }
+#ifdef PDSC_TUNING
     if (trace_path) {
         static long long h[16 * 256];
         cudaDeviceSynchronize();
@@ -982,6 +1004,7 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
         }
         cudaFree(p.trace);
     }
+#endif
     count_launches(1);
     return check_launch("nonlocal_attn(tcgen05 ping-pong)");
 }
@@ -1001,11 +1024,7 @@ int launch_attn_pp(const float* q, const float* k, const float* v, int64_t ld, c
     int* counters;
     int n_counters;
     attn_pp_tile_pointers(ws, B, N, &Qw, &Kw, &Vw, &Pw, &counters, &n_counters);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(attn_pp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 4);
-        attr_set = true;
-    }
+    opt_in_smem<attn_pp_prep_kernel>(128 * 129 * 4);
     const float qscale = 1.4426950408889634f / sqrtf((float)C);
     attn_pp_prep_kernel<<<dim3(NT128, B), 256, 128 * 129 * 4, st>>>(q, k, v, ld, src, tgt, N, NT128, qscale, 1.0f / sigma_spat,
                                                                       Qw, Kw, Vw, Pw, counters, n_counters);

@@ -25,6 +25,32 @@ void count_launches(int n);   // kernels enqueued, read back through pdsc_launch
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 int num_sms();
 
+// Opt-in to more than 48 KB of dynamic shared memory.  The attribute is per device (and per function), so the cache is
+// keyed by the current device: a process that runs on cuda:0 and then on cuda:1 opts in on both.
+template <auto Kernel>
+inline void opt_in_smem(int bytes) {
+    static thread_local int set_bytes[64];      // zero-initialised; per kernel instantiation
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && set_bytes[dev] >= bytes) return;
+    cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (dev >= 0 && dev < 64) set_bytes[dev] = bytes;
+}
+
+// ---- tuning / debugging knobs ----------------------------------------------------------------
+// The shipped library (libpointdsc_b200.so) is built WITHOUT PDSC_TUNING: every knob is its compile-time default and the
+// environment is never read.  The tests and scripts/ that exercise other launch shapes load libpointdsc_b200_tuning.so,
+// the same sources built with -DPDSC_TUNING, where `tuning_int("PDSC_X", d)` reads the environment variable per call.
+#ifdef PDSC_TUNING
+int tuning_int(const char* name, int dflt);
+const char* tuning_str(const char* name);
+constexpr bool kTuningBuild = true;
+#else
+inline int tuning_int(const char*, int dflt) { return dflt; }
+inline const char* tuning_str(const char*) { return nullptr; }
+constexpr bool kTuningBuild = false;
+#endif
+
 // ---- warp helpers ---------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -206,12 +232,8 @@ int launch_seed_hypotheses(const float* normed, const float* src, const float* t
                            int N, int C, int S, int k, float sigma, float sigma_spat, int num_iterations,
                            float* seed_trans, float* weights, int32_t* iters, void* ws, size_t ws_bytes,
                            cudaStream_t st);
-size_t attn_workspace(int B, int N, int C, int mode);
 int launch_attn_fp32(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
                      float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, cudaStream_t st);
-int launch_attn_tc(const float* q, const float* k, const float* v, int64_t ld, const float* src, const float* tgt,
-                   float* out, int64_t ld_out, int B, int N, int C, float sigma_spat, int mode, void* ws,
-                   size_t ws_bytes, cudaStream_t st);
 int launch_nn_match(const float* A, const float* Bm, int P, int Na, int Nb, int D, int metric, int64_t* idx1, int64_t* idx2,
                     float* val1, float* val2, cudaStream_t st);
 int launch_mutual_corr(const int64_t* idx_ab, const int64_t* idx_ba, int P, int Na, int Nb, int use_mutual, int64_t* corr,

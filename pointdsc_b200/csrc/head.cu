@@ -132,11 +132,7 @@ int launch_feature_head(const float* feat, long long rows, int C, int H1, int H2
     p.feat = feat; p.w1 = w1t; p.b1 = b1; p.w2 = w2t; p.b2 = b2; p.w3 = w3; p.b3 = b3;
     p.normed = normed; p.conf = conf; p.rows = rows; p.eps = eps;
     const int smem = (int)sizeof(float) * (128 * HD_PITCH + HD_C * HD_H + HD_H * HD_H + 3 * HD_H + 128 + 128 * (HD_H + 1));
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(feature_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_set = true;
-    }
+    opt_in_smem<feature_head_kernel>(smem);
     feature_head_kernel<<<(unsigned)((rows + 127) / 128), HD_THREADS, smem, st>>>(p);
     count_launches(1);
     return check_launch("feature_head");

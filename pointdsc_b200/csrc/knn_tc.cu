@@ -211,11 +211,7 @@ int launch_knn_gram_tc(const float* normed, const int64_t* seeds, int B, int N, 
     p.N = N; p.S = S; p.nh = nh; p.NT = (N + 127) / 128;
     p.items = (long long)B * nh * p.NT;
     const int smem = (int)(KT_IMG + KT_STAGE + 1024);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(knn_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_set = true;
-    }
+    opt_in_smem<knn_gram_tc_kernel>(smem);
     long long grid = num_sms();
     if (grid > p.items) grid = p.items;
     knn_gram_tc_kernel<<<(int)grid, KT_THREADS, smem, st>>>(p);

@@ -271,11 +271,7 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     if (p.n_bias * sizeof(float) > 1024) { set_error("mlp_chain: too many bias entries"); return PDSC_ERR_ARG; }
     const int smem = (int)(p.w_bytes + 1024 + ML_STAGE_BYTES + ((add_out || y) ? ML_STAGE_BYTES : 0) + 1024);
     if (smem > 227 * 1024) { set_error("mlp_chain: chain does not fit in shared memory (%d bytes)", smem); return PDSC_ERR_ARG; }
-    static int smem_set = 0;
-    if (smem > smem_set) {
-        cudaFuncSetAttribute(mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        smem_set = smem;
-    }
+    opt_in_smem<mlp_chain_kernel>(smem);
     const long long n_tiles = (rows + 127) / 128;
     long long grid = num_sms();
     if (grid > n_tiles) grid = n_tiles;

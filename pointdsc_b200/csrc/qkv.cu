@@ -224,11 +224,7 @@ int launch_qkv_pack(const float* y, const void* wpack, const float* bias, const 
     p.qscale = 1.4426950408889634f / sqrtf((float)C);
     p.inv_sigma = 1.0f / sigma_spat;
     const int smem = (int)(3 * QK_IMG + 1024);   // weights + one operand/image buffer per warp group
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(qkv_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_set = true;
-    }
+    opt_in_smem<qkv_pack_kernel>(smem);
     const long long n_tiles = (long long)B * p.NT128;
     long long gx = num_sms() / 3;
     if (gx > n_tiles) gx = n_tiles;

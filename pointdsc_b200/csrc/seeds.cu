@@ -191,12 +191,7 @@ int launch_pick_seeds(const float* src, const float* scores, int B, int N, float
                                                      align_up(sizeof(int32_t) * (size_t)B * N, 256));
         smem = 0;
     } else {
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(seed_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(sizeof(unsigned long long) * SORT_SMEM_MAX_ELEMS));
-            attr_set = true;
-        }
+        opt_in_smem<seed_order_kernel>((int)(sizeof(unsigned long long) * SORT_SMEM_MAX_ELEMS));
     }
     seed_order_kernel<<<B, 1024, smem, st>>>(scores, suppressed, N, S, p2, gbuf, seeds, is_local_max, n_pos);
     count_launches(2);
@@ -500,9 +495,9 @@ int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int
         return PDSC_ERR_WORKSPACE;
     }
     float* D = reinterpret_cast<float*>(ws);
-    // C == 128: Gram on the tensor cores (knn_tc.cu); PDSC_KNN_FP32=1 keeps the fp32 CUDA-core Gram (tests compare the two)
-    const char* env_fp32 = getenv("PDSC_KNN_FP32");
-    const bool force_fp32 = env_fp32 && atoi(env_fp32) != 0;
+    // C == 128: Gram on the tensor cores (knn_tc.cu); PDSC_KNN_FP32=1 (tuning build) keeps the fp32 CUDA-core Gram (tests
+    // compare the two)
+    const bool force_fp32 = tuning_int("PDSC_KNN_FP32", 0) != 0;
     if (C == 128 && !force_fp32) {
         void* img = reinterpret_cast<char*>(ws) + align_up(sizeof(float) * (size_t)B * S * N, 1024);
         const int rc = launch_knn_gram_tc(normed, seeds, B, N, S, D, img, st);
@@ -514,11 +509,7 @@ int launch_seed_knn(const float* normed, const int64_t* seeds, int B, int N, int
     }
     if (N <= KS_SMEM_KEYS) {
         const int smem = (int)sizeof(unsigned int) * N;
-        static int smem_set = 0;
-        if (smem > 40 * 1024 && smem > smem_set) {
-            cudaFuncSetAttribute(knn_select_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(unsigned int) * KS_SMEM_KEYS);
-            smem_set = (int)sizeof(unsigned int) * KS_SMEM_KEYS;
-        }
+        if (smem > 40 * 1024) opt_in_smem<knn_select_kernel<true>>((int)sizeof(unsigned int) * KS_SMEM_KEYS);
         knn_select_kernel<true><<<B * S, KS_THREADS, smem, st>>>(D, N, S, k, knn_idx, knn_dist);
     } else {
         knn_select_kernel<false><<<B * S, KS_THREADS, 0, st>>>(D, N, S, k, knn_idx, knn_dist);

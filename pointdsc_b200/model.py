@@ -5,12 +5,13 @@ Same constructor keywords (models/PointDSC.py:81-91), same module tree and ``sta
 contract (:128-197), so ``model.load_state_dict(torch.load('model_best.pkl'))`` and
 ``res = model(data)`` work unchanged.  What differs is underneath:
 
-* the 1x1-conv MLPs run as channel-last fp32 GEMMs (BatchNorm folded, q/k/v fused into one
-  projection) -- still torch ops, as BASELINE.json's north_star prescribes;
-* everything else goes through the C ABI of ``libpointdsc_b200.so`` (hand-written sm_100a
-  kernels): compatibility-weighted attention without the N x N matrix, NMS seed picking,
-  seed-row feature kNN, per-seed spectral matching + Kabsch, hypothesis scoring and the whole
-  post-refinement loop.  There is no CPU or pure-PyTorch fallback: inputs must be CUDA tensors.
+* everything but ``layer0`` (a 6 -> 128 torch addmm) goes through the C ABI of ``libpointdsc_b200.so`` (hand-written
+  sm_100a kernels): per encoder layer PointCN (``pdsc_mlp_chain``, BatchNorm folded), the q/k/v projections written
+  straight into the attention operand tiles (``pdsc_qkv_pack``), the compatibility-weighted attention without the
+  N x N matrix, and fc_message + residual (``pdsc_mlp_chain``); then the normalisation + classifier head, NMS seed
+  picking, seed-row feature kNN, per-seed spectral matching + Kabsch, hypothesis scoring and the whole post-refinement
+  loop.  ``POINTDSC_MLP_MODE=split16|fp32`` keeps the 1x1 convs as torch GEMMs (the form BASELINE.json's north_star
+  names).  There is no CPU or pure-PyTorch fallback: inputs must be CUDA tensors.
 
 Batches: the reference's test path only supports batch size 1 (:210, :414); here ``[B,N,.]``
 means B independent pairs and the result equals B separate reference runs.
@@ -26,7 +27,9 @@ import torch.nn.functional as F
 
 from . import _cabi
 
-_MODE_NAMES = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "fp16": _cabi.ATTN_FP16}
+_MODE_NAMES = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16x3": _cabi.ATTN_SPLIT16X3,
+               "fp16": _cabi.ATTN_FP16}
+_MLP_MODES = ("fused", "split16", "fp32")
 
 
 def _pointwise_mlp(dims, norm, last_act):
@@ -113,12 +116,17 @@ class PointDSC(nn.Module):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
         # kernel selection for the attention contraction (include/pointdsc_b200.h PDSC_ATTN_*)
-        self.attn_mode = _MODE_NAMES[os.environ.get("POINTDSC_ATTN_MODE", "split16")]
-        # how the 1x1-conv stacks run: "fused" = PointCN and fc_message(+residual) as on-chip tcgen05 chains
-        # (pdsc_mlp_chain), the q/k/v projection as one library GEMM on packed fp16 hi/lo operands;
-        # "split16" = every layer a library GEMM on packed operands (torch.mm, fp32 accumulation/output);
+        attn_mode = os.environ.get("POINTDSC_ATTN_MODE", "split16")
+        if attn_mode not in _MODE_NAMES:
+            raise ValueError(f"POINTDSC_ATTN_MODE={attn_mode!r}: expected one of {sorted(_MODE_NAMES)}")
+        self.attn_mode = _MODE_NAMES[attn_mode]
+        # how the 1x1-conv stacks run: "fused" (default) = PointCN and fc_message(+residual) as on-chip tcgen05 chains
+        # (pdsc_mlp_chain) and the q/k/v projections inside pdsc_qkv_pack, no library GEMM on the layer path;
+        # "split16" = every layer a library GEMM on packed fp16 hi/lo operands (torch.mm, fp32 accumulation/output);
         # "fp32" = plain fp32 addmm.  All three are fp32-grade accurate.
         self.mlp_mode = os.environ.get("POINTDSC_MLP_MODE", "fused")
+        if self.mlp_mode not in _MLP_MODES:
+            raise ValueError(f"POINTDSC_MLP_MODE={self.mlp_mode!r}: expected one of {_MLP_MODES}")
         self._packed = None
         self._ws = _cabi.Workspace()
 
@@ -200,6 +208,8 @@ class PointDSC(nn.Module):
         C = self.num_channels
         W, b = P["layer0"]
         feat = torch.addmm(b, corr_pos.reshape(B * N, -1), W)
+        if self.mlp_mode not in _MLP_MODES:          # (the attribute may have been set after construction)
+            raise ValueError(f"mlp_mode={self.mlp_mode!r}: expected one of {_MLP_MODES}")
         if self.mlp_mode == "fused" and feat.is_cuda and C == 128:
             return self._encode_fused(P, feat, src, tgt, B, N, C)
         if self.mlp_mode in ("split16", "fused") and feat.is_cuda and C % 16 == 0:

@@ -10,4 +10,4 @@ for g in ${GRIDS:-sk 0}; do
   timeout 120 python scripts/prof_attn.py fp16 16 5000 10
 done
 unset PDSC_ATTN_GRID
-echo "== old kernel"; PDSC_ATTN_IMPL=tc timeout 120 python scripts/prof_attn.py split16 16 5000 10
+

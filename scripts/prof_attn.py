@@ -3,7 +3,10 @@ import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from pointdsc_b200 import _cabi
-mode = {"fp32": 0, "split16": 1, "fp16": 2}[sys.argv[1] if len(sys.argv) > 1 else "split16"]
+mode = {"fp32": 0, "split16": 1, "fp16": 2, "split16x3": 3}[sys.argv[1] if len(sys.argv) > 1 else "split16"]
+if any(k.startswith("PDSC_") for k in os.environ):      # knobs only exist in the -DPDSC_TUNING build
+    _cabi.use_tuning_library().__enter__()
+    print("tuning library:", {k: v for k, v in os.environ.items() if k.startswith("PDSC_")})
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 N = int(sys.argv[3]) if len(sys.argv) > 3 else 5000
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
@@ -23,3 +26,14 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
 print(f"mode {mode} B={B} N={N}: {ms:.3f} ms per call (prep+main), {4.0 * N * N * C * B / ms / 1e9:.1f} TFLOP/s algorithmic")
+if mode != 0:
+    # main kernel alone, on the operand tiles the last call left in the workspace
+    ws = _cabi._ws(_cabi.workspace_bytes(_cabi.OP_NONLOCAL_ATTN, B, N, C, mode=mode), qkv.device, None)
+    e0.record()
+    for _ in range(reps):
+        out2 = _cabi.nonlocal_attn_packed(ws, B, N, C, mode=mode)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    print(f"mode {mode} B={B} N={N}: {ms:.3f} ms per call (main kernel only), {4.0 * N * N * C * B / ms / 1e9:.1f} TFLOP/s algorithmic; "
+          f"same result as prep+main: {bool(torch.equal(out, out2))}")

@@ -33,10 +33,20 @@ def load_golden(name):
     return meta, arrays
 
 
-GOLDEN_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("next_", "front_", "full_")))   # next_*: test_next_oracle.py, front_*: test_frontend_oracle.py, full_*: lean full-size fixtures
+GOLDEN_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("next_", "front_", "full_", "batch_")))   # next_*: test_next_oracle.py, front_*: test_frontend_oracle.py, full_*: lean full-size fixtures
+BATCH_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.startswith("batch_") and f.endswith(".npz"))   # 16-pair batches of BASELINE configs[1], configs[2]
 FULL_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.startswith("full_") and f.endswith(".npz"))
 
 
 @pytest.fixture(scope="session")
 def golden():
     return load_golden
+
+
+@pytest.fixture
+def tuning_lib():
+    """Routes the test's C-ABI calls to libpointdsc_b200_tuning.so, the -DPDSC_TUNING build that reads the PDSC_* knobs from
+    the environment (the product library ignores them)."""
+    from pointdsc_b200 import _cabi
+    with _cabi.use_tuning_library() as lib:
+        yield lib

@@ -235,7 +235,7 @@ def test_seed_knn_ties_and_long_rows(N, copies):
 
 
 @pytest.mark.parametrize("N,S", [(5000, 500), (1000, 100), (777, 300), (10000, 1000)])
-def test_seed_knn_tensor_core_gram_vs_fp32_gram(N, S, monkeypatch):
+def test_seed_knn_tensor_core_gram_vs_fp32_gram(N, S, monkeypatch, tuning_lib):
     """The tcgen05 Gram (fp16 hi/lo split, fp32 accumulate) against the fp32 CUDA-core Gram of the same library:
     distances within 2e-6, neighbour lists equal except where the fp32 distances are closer than that."""
     from pointdsc_b200 import _cabi
@@ -371,12 +371,16 @@ def _attn_ref(qkv, src, tgt, sigma):
     return torch.cat(outs)
 
 
+@pytest.mark.parametrize("mode", ["split16", "split16x3"])
 @pytest.mark.parametrize("grid", [None, "0", "5", "7"])
 @pytest.mark.parametrize("N", [128, 1, 100, 129, 256, 257, 700, 1100])
-def test_attention_split16_vs_oracle(N, grid, monkeypatch):
+def test_attention_split16_vs_oracle(N, grid, mode, monkeypatch, tuning_lib):
     """grid: None = stream-K over all SMs (partials + last-arriver combine), "0" = one CTA per 256-row
-    block (no partials), "5"/"7" = a few CTAs whose ranges cut blocks at odd places."""
+    block (no partials), "5"/"7" = a few CTAs whose ranges cut blocks at odd places.  mode: the default term set
+    (P_hi only, integer reference maximum) and the three-term form."""
     from pointdsc_b200 import _cabi
+    if mode == "split16x3" and grid in ("0", "7"):
+        pytest.skip("three-term form: stream-K and one odd grid are enough")
     if grid is None:
         monkeypatch.delenv("PDSC_ATTN_GRID", raising=False)
     else:
@@ -387,18 +391,19 @@ def test_attention_split16_vs_oracle(N, grid, monkeypatch):
     src = torch.rand(B, N, 3, generator=g)
     tgt = src + 0.05 * torch.randn(B, N, 3, generator=g)
     d = cu(qkv)
-    out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1, mode=_cabi.ATTN_SPLIT16)
+    out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1,
+                              mode=_cabi.ATTN_SPLIT16 if mode == "split16" else _cabi.ATTN_SPLIT16X3)
     torch.cuda.synchronize()
     ref = _attn_ref(qkv, src, tgt, 0.1)
     err = (out.cpu() - ref).abs().max().item()
-    print(f"split16 attention N={N} grid={grid}: max abs err {err:.3e}")
+    print(f"{mode} attention N={N} grid={grid}: max abs err {err:.3e}")
     assert err < 5e-5
 
 
 @pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation", "chain3", "chain1"])
 @pytest.mark.parametrize("grid", [None, "3"])
 @pytest.mark.parametrize("N", [100, 257, 700, 1300])
-def test_attention_launch_variants_vs_oracle(N, grid, variant, monkeypatch):
+def test_attention_launch_variants_vs_oracle(N, grid, variant, monkeypatch, tuning_lib):
     """The other instantiations of the attention kernel that live in the tree: the cluster-of-2 launch shape with TMA
     multicast of the K / V tiles (PDSC_ATTN_CLUSTER=2; odd block counts leave one CTA of the last cluster on a phantom
     block), the debug instantiation (PDSC_ATTN_DBG=8: no knob set, same arithmetic) and the chain limit that cuts every CTA

@@ -24,6 +24,30 @@ def test_library_exports_every_declared_symbol():
     assert lib.pdsc_version() >= 100
 
 
+def test_product_library_reads_no_tuning_knob():
+    """The debug / tuning knobs exist only in libpointdsc_b200_tuning.so (-DPDSC_TUNING); the shipped library does not even
+    contain their names, so no environment variable can change its arithmetic or launch shape."""
+    blob = open(_cabi.LIB_PATH, "rb").read()
+    assert b"PDSC_ATTN_" not in blob and b"PDSC_KNN_" not in blob
+    tuning = open(_cabi.TUNING_LIB_PATH, "rb").read()
+    for knob in (b"PDSC_ATTN_GRID", b"PDSC_ATTN_CHAIN", b"PDSC_ATTN_CLUSTER", b"PDSC_ATTN_DBG", b"PDSC_ATTN_PV_TERMS",
+                 b"PDSC_KNN_FP32"):
+        assert knob in tuning, knob
+    with _cabi.use_tuning_library() as lib:
+        assert _cabi.is_tuning_library() and lib.pdsc_version() >= 100
+    assert not _cabi.is_tuning_library()
+
+
+def test_mode_typos_are_refused(monkeypatch):
+    monkeypatch.setenv("POINTDSC_MLP_MODE", "fuse")
+    with pytest.raises(ValueError, match="POINTDSC_MLP_MODE"):
+        PointDSC(num_layers=1)
+    monkeypatch.delenv("POINTDSC_MLP_MODE")
+    monkeypatch.setenv("POINTDSC_ATTN_MODE", "split")
+    with pytest.raises(ValueError, match="POINTDSC_ATTN_MODE"):
+        PointDSC(num_layers=1)
+
+
 def test_workspace_queries_do_not_need_a_gpu():
     need = _cabi.workspace_bytes(_cabi.OP_SEED_KNN, B=2, N=1000, C=128, S=100, k=40)      # distances + seed operand images
     assert 2 * 100 * 1000 * 4 + 2 * 131072 <= need <= 2 * 100 * 1000 * 4 + 2 * 131072 + 1024
