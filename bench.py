@@ -43,10 +43,12 @@ def parse_args():
     ap.add_argument("--pairs", type=int, default=16, help="pairs per step per GPU")
     ap.add_argument("--n", type=int, default=5000, help="correspondences per pair")
     ap.add_argument("--family", default="3dmatch", choices=["3dmatch", "kitti"])
-    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "fp16"])
+    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "split16x3", "fp16"])
     ap.add_argument("--cpu-pairs", type=int, default=3, help="pairs in the cpu_baseline sample (first is warm-up)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--weight-seed", type=int, default=99, help="seed of the synthetic weights (oracle/synth.py)")
+    ap.add_argument("--no-config4", action="store_true", help="skip the N=50000 row-sharded power-iteration leg")
+    ap.add_argument("--config4-n", type=int, default=50000)
     return ap.parse_args()
 
 
@@ -55,10 +57,15 @@ def workload_name(args):
            f"{NUM_LAYERS} layers, C={C}, seeded weights (seed {args.weight_seed})"
 
 
+NCU_ATTN_PROFILE = "profiles/r02_ncu_attn_pp.json"
+
+
 def ncu_traffic(args):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE attention launch, from the committed ncu --set full
-    capture of the same workload (profiles/r01_ncu_attn_pp.json); None for other workloads."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_attn_pp.json")
+    capture of the same workload and kernel (NCU_ATTN_PROFILE); None for other workloads or when it is absent.  A bench
+    run cannot measure DRAM traffic itself (that needs the profiler, and a number taken under a profiler is not a bench
+    value), so the line says where the figure comes from (roofline.traffic_source)."""
+    path = os.path.join(ROOT, NCU_ATTN_PROFILE)
     if not (os.path.exists(path) and args.pairs == 16 and args.n == 5000 and args.mode == "split16"):
         return None
     try:
@@ -155,31 +162,30 @@ def make_inputs(args, rank):
     return cfg, batch, sd
 
 
-def golden_check(args, res):
-    """Pair 0 of the default workloads is the full-size golden case (tests/golden/full_*.npz: outputs of the unmodified
-    reference, oracle/gen_golden.py --full).  Compares the LAST timed step's result for that pair with it (outside the timed
-    region; reads a committed fixture, runs nothing from oracle/)."""
+def golden_check(args, res, batch, rank):
+    """The default workloads are exactly the 16-pair golden batches (tests/golden/batch_*.npz: outputs of the unmodified
+    reference for EVERY pair, oracle/gen_golden.py --batch).  Compares the LAST timed step's result with them, all pairs,
+    outside the timed region (reads a committed fixture; tests/parity.py holds the comparison rules)."""
     import json as _json
     import numpy as np
-    name = {("3dmatch", 5000): "full_3dmatch_n5000_l12", ("kitti", 10000): "full_kitti_n10000_l12"}.get((args.family, args.n))
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", f"{name}.npz")
-    if name is None or not os.path.exists(path):
+    name = {("3dmatch", 5000): "batch_3dmatch_n5000_l12", ("kitti", 10000): "batch_kitti_n10000_l12"}.get((args.family, args.n))
+    path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
+    if name is None or rank != 0 or args.pairs != 16 or not os.path.exists(path):
         return None
     z = np.load(path)
     meta = _json.loads(bytes(z["meta"]).decode())
     if meta["weight_seed"] != args.weight_seed or meta["num_layers"] != NUM_LAYERS:
         return None
-    T = res["final_trans"][0].double().cpu()
-    G = torch.from_numpy(z["final_trans"])[0].double()
-    rot = float(torch.rad2deg(2 * torch.asin(torch.clamp(torch.linalg.matrix_norm(T[:3, :3] - G[:3, :3]) / (2 * 2 ** 0.5), max=1.0))))
-    return {"case": name, "against": "unmodified reference (committed golden vector), pair 0 of the timed batch",
-            "rot_err_deg": rot, "trans_err_m": float(torch.norm(T[:3, 3] - G[:3, 3])),
-            "max_abs_dconf": float((res["confidence"][0].cpu() - torch.from_numpy(z["confidence"])[0]).abs().max()),
-            "max_abs_dconf_vs_float64_reference": {
-                "ours": float((res["confidence"][0].cpu().double() - torch.from_numpy(z["confidence_f64"])[0]).abs().max()),
-                "fp32_reference": float((torch.from_numpy(z["confidence"])[0].double() - torch.from_numpy(z["confidence_f64"])[0]).abs().max())},
-            "label_mismatches": int((res["final_labels"][0].cpu() != torch.from_numpy(z["final_labels"])[0].float()).sum()),
-            "tolerance": "rot <= 0.01 deg, trans <= 1e-4 m, conf <= 1e-4"}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import synth
+    from parity import batch_parity_report
+    g = {k: torch.from_numpy(z[k]) for k in z.files if k != "meta"}
+    rep = batch_parity_report(name, meta, g, batch, res, synth.CONFIGS[args.family])
+    rows = rep.pop("pairs")
+    rep["pairs_compared"] = len(rows)
+    rep["worst_pair_by_dconf"] = max(rows, key=lambda r: r["max_abs_dconf"])["pair_seed"]
+    rep["ok"] = not rep["failures"]
+    return rep
 
 
 def cpu_baseline(args, cfg, batch, sd, n_pairs):
@@ -262,7 +268,8 @@ def main():
                      nms_radius=cfg["nms_radius"]).eval()
     model.load_state_dict(sd, strict=True)
     model = model.to(dev)
-    model.attn_mode = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "fp16": _cabi.ATTN_FP16}[args.mode]
+    model.attn_mode = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16x3": _cabi.ATTN_SPLIT16X3,
+                       "fp16": _cabi.ATTN_FP16}[args.mode]
 
     keys = ("corr_pos", "src_keypts", "tgt_keypts")
     host = {k: batch[k].pin_memory() for k in keys}
@@ -325,35 +332,26 @@ def main():
     barrier()
     attn_events.clear()
     sampler.recording = True
-    # A timed region is EXACTLY args.steps consecutive steps between two events.  A host-side stall (another process on the
-    # box, a slow NVML query, a page-in) of tens of milliseconds inside it is not GPU work: when one step of the region
-    # took more than twice the median step (on any rank), the whole region is measured again (at most twice) and the
-    # line says so (config.retimed_after_host_stall).
-    def timed_region(step_fn, on_start=None):
-        retimed = 0
-        while True:
-            if on_start is not None:
-                on_start()
-            l0 = _cabi.kernel_launches()
-            marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-            t0 = time.perf_counter()
-            marks[0].record()
-            out = None
-            for i in range(args.steps):
-                out = step_fn()
-                marks[i + 1].record()
-            barrier()
-            wall = time.perf_counter() - t0
-            n_launch = _cabi.kernel_launches() - l0
-            per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
-            stall = torch.tensor([1.0 if args.steps >= 3 and per_step[-1] > 2.0 * per_step[len(per_step) // 2] else 0.0], device=dev)
-            if dist is not None:
-                dist.all_reduce(stall, op=dist.ReduceOp.MAX)           # every rank takes the same decision
-            if stall.item() == 0.0 or retimed >= 2:
-                return marks[0].elapsed_time(marks[-1]), wall, n_launch, retimed, out
-            retimed += 1
+    # A timed region is EXACTLY args.steps consecutive steps between two events, measured ONCE: nothing is re-measured or
+    # discarded.  Every step is also bracketed by its own events and the line reports min / median / max per step, so a
+    # host-side stall inside the region (another process on the box, a page-in) is visible instead of being filtered out.
+    def timed_region(step_fn):
+        l0 = _cabi.kernel_launches()
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        t0 = time.perf_counter()
+        marks[0].record()
+        out = None
+        for i in range(args.steps):
+            out = step_fn()
+            marks[i + 1].record()
+        barrier()
+        wall = time.perf_counter() - t0
+        n_launch = _cabi.kernel_launches() - l0
+        per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
+        stats = {"min": per_step[0], "median": statistics.median(per_step), "max": per_step[-1]}
+        return marks[0].elapsed_time(marks[-1]), wall, n_launch, stats, out
 
-    dev_ms, t_wall, launches, retimed, res = timed_region(step_resident, on_start=attn_events.clear)
+    dev_ms, t_wall, launches, step_stats, res = timed_region(step_resident)
     setattr(_cabi, attn_name, orig_attn)
     attn_ms = [a.elapsed_time(b) for a, b in attn_events]
 
@@ -375,7 +373,7 @@ def main():
     for _ in range(max(1, args.warmup // 2)):
         step_e2e()
     barrier()
-    e2e_ms, _, _, retimed_e2e, _ = timed_region(step_e2e)
+    e2e_ms, _, _, e2e_step_stats, _ = timed_region(step_e2e)
     clocks = sampler.stop()
 
     # -------- reduce over ranks (max time) ---------------------------------------------------------
@@ -392,17 +390,18 @@ def main():
         flops_per_launch = 4.0 * args.n * args.n * C * args.pairs          # QK^T + PV, per layer, per batch
         avg_attn_ms = sum(attn_ms) / max(1, len(attn_ms))
         achieved = flops_per_launch / (avg_attn_ms * 1e-3) / 1e12
+        terms = {"fp16": 1.0, "split16": 2.5, "split16x3": 3.0, "fp32": 0.0}[args.mode]
         roofline = {"bound": "tensor", "kernel": f"pdsc_{attn_name}[{args.mode}]", "achieved": achieved,
                     "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_sustained"],
-                    "traffic": ncu_traffic(args), "traffic_note": "dram bytes of the main attention kernel per launch (ncu --set full, "
-                    "profiles/r01_ncu_attn_pp.json); algorithmic HBM bytes per launch = 4*B*N*C*4", "peak_source": pk["source"] + ", bf16 sustained",
+                    "traffic": ncu_traffic(args), "traffic_source": f"committed capture {NCU_ATTN_PROFILE} (ncu --set full of this kernel on "
+                    "this workload; not measured by this run); algorithmic HBM bytes per launch = 4*B*N*C*4", "peak_source": pk["source"] + ", bf16 sustained",
                     "algorithmic_flops_per_launch": flops_per_launch, "avg_launch_ms": avg_attn_ms,
                     "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms,
-                    # split16 issues three fp16 products per contraction (hi*hi + hi*lo + lo*hi) to reach fp32-grade results:
-                    # the tensor pipe does 3x the algorithmic work, so `frac` cannot exceed 1/3
-                    "mma_terms": 1 if args.mode == "fp16" else (3 if args.mode == "split16" else 0),
-                    "issued": achieved * (3 if args.mode == "split16" else 1) if args.mode != "fp32" else None,
-                    "issued_frac": achieved * (3 if args.mode == "split16" else 1) / pk["bf16_sustained"] if args.mode != "fp32" else None}
+                    # fp32-grade results from fp16 tensor-core products: Q K^T as hi*hi + hi*lo + lo*hi (3 terms), P V as
+                    # P_hi*(V_hi + V_lo) (2 terms; 3 in split16x3): the tensor pipe does `mma_terms_avg` x the algorithmic
+                    # work, so `frac` cannot exceed 1 / mma_terms_avg
+                    "mma_terms_avg": terms, "issued": achieved * terms if terms else None,
+                    "issued_frac": achieved * terms / pk["bf16_sustained"] if terms else None}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -411,16 +410,20 @@ def main():
             "config": {"workload": workload_name(args), "family": args.family, "pairs_per_step_per_gpu": args.pairs,
                        "N": args.n, "num_layers": NUM_LAYERS, "attn_mode": args.mode,
                        "l2": "256 MB buffer rewritten between steps (inside the timed region)",
-                       "extra_warmup_steps_until_steady": settle_steps, "retimed_after_host_stall": {"resident": retimed, "e2e": retimed_e2e},
+                       "extra_warmup_steps_until_steady": settle_steps,
+                       "env": {k: v for k, v in sorted(os.environ.items()) if k.startswith(("PDSC_", "POINTDSC_"))},
+                       "library": os.path.basename(_cabi.LIB_PATH) + " (reads no environment variable; knobs exist only in the -DPDSC_TUNING build, which bench.py never loads)",
                        "parallelism": f"pairs sharded over {world} GPU(s), no communication"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "ms_per_step": e2e_ms / args.steps},
+                    "ms_per_step": e2e_ms / args.steps, "step_ms": e2e_step_stats},
+            "step_ms": step_stats,
+            "retimed": 0,
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": roofline,
             "wall_s_timed_region": t_wall,
         }
-        chk = golden_check(args, res)
+        chk = golden_check(args, res, batch, rank)
         if chk is not None:
             line["parity_check"] = chk
         if world == 1 and not args.no_cpu_baseline:

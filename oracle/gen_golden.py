@@ -23,6 +23,8 @@ CASES = {
     "g1_3dmatch_n1000_l12": ("3dmatch", 1000, 12, 7, 1234),
     "g2_kitti_n800_l6": ("kitti", 800, 6, 107, 4321),
     "g3_3dmatch_n2000_l12": ("3dmatch", 2000, 12, 3, 99),
+    # stress weights (synth.STRESS): sharp attention (|logit| up to ~20 in log2 units), confidences spanning > 1
+    "g4_3dmatch_n2000_l12_stress": ("3dmatch", 2000, 12, 5, 99, synth.STRESS),
 }
 
 
@@ -33,23 +35,31 @@ FULL_CASES = {
     # 1234 every confidence is negative at 12 layers and the reference's argsort fills the seed list from exact ties)
     "full_3dmatch_n5000_l12": ("3dmatch", 5000, 12, 0, 99),
     "full_kitti_n10000_l12": ("kitti", 10000, 12, 100, 99),
+    "full_3dmatch_n5000_l12_stress": ("3dmatch", 5000, 12, 0, 99, synth.STRESS),
 }
 
 
+def weight_kwargs(name):
+    c = CASES.get(name) or FULL_CASES[name]
+    return dict(c[5]) if len(c) > 5 else {}
+
+
 def case_inputs(name):
-    fam, N, L, pair_seed, w_seed = (CASES.get(name) or FULL_CASES[name])
+    fam, N, L, pair_seed, w_seed = (CASES.get(name) or FULL_CASES[name])[:5]
     cfg = synth.CONFIGS[fam]
-    sd = synth.make_state_dict(w_seed, num_layers=L, sigma_d=cfg["sigma_d"])
+    sd = synth.make_state_dict(w_seed, num_layers=L, sigma_d=cfg["sigma_d"], **weight_kwargs(name))
     pair = synth.make_pair(pair_seed, N, **cfg)
     ctor = dict(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
                 nms_radius=cfg["nms_radius"])
     return cfg, sd, pair, ctor
 
 
-def main():
+def main(only=None):
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     torch.set_num_threads(8)
     for name in CASES:
+        if only and only not in name:
+            continue
         cfg, sd, pair, ctor = case_inputs(name)
         model = ref_harness.build_reference_model(sd, **ctor)
         rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
@@ -61,9 +71,10 @@ def main():
             "final_trans": rec["final_trans"],
             "refine_sizes": torch.tensor(rec["refine_sizes"], dtype=torch.int64),
             "normed_features": rec["normed_features"],
+            "power_iters": torch.tensor([rec["power_iters"]], dtype=torch.int64),
         }
         meta = dict(case=name, family=CASES[name][0], N=CASES[name][1], num_layers=CASES[name][2],
-                    pair_seed=CASES[name][3], weight_seed=CASES[name][4], ctor=ctor,
+                    pair_seed=CASES[name][3], weight_seed=CASES[name][4], ctor=ctor, weight_kwargs=weight_kwargs(name),
                     torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing)")
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"),
                             meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8),
@@ -72,9 +83,11 @@ def main():
               "conf [%.4f, %.4f]" % (rec["confidence"].min(), rec["confidence"].max()))
 
 
-def main_full():
+def main_full(only=None):
     torch.set_num_threads(os.cpu_count())
     for name in FULL_CASES:
+        if only and only not in name:
+            continue
         cfg, sd, pair, ctor = case_inputs(name)
         model = ref_harness.build_reference_model(sd, **ctor)
         rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
@@ -93,10 +106,11 @@ def main_full():
             "seed_trans": rec["seed_trans"], "inlier_count": torch.round(rec["seed_fitness"] * FULL_CASES[name][1]).to(torch.int32),
             "initial_trans": rec["initial_trans"], "final_labels": rec["final_labels"].to(torch.uint8),
             "final_trans": rec["final_trans"], "refine_sizes": torch.tensor(rec["refine_sizes"], dtype=torch.int64),
+            "power_iters": torch.tensor([rec["power_iters"]], dtype=torch.int64),
         }
         meta = dict(case=name, family=FULL_CASES[name][0], N=FULL_CASES[name][1], num_layers=FULL_CASES[name][2],
                     pair_seed=FULL_CASES[name][3], weight_seed=FULL_CASES[name][4], ctor=ctor, k=k,
-                    torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing)")
+                    weight_kwargs=weight_kwargs(name), torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing)")
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"),
                             meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8),
                             **{k_: v.numpy() for k_, v in arrays.items()})
@@ -105,6 +119,58 @@ def main_full():
               os.path.getsize(os.path.join(GOLDEN_DIR, name + ".npz")) // 1024, "KiB")
 
 
+# The whole timed batches of bench.py / BASELINE configs[1] and configs[2]: 16 pairs each (pair seeds 0..15 and 100..115,
+# weight seed 99), every pair through the unmodified reference one at a time (its test path is batch-size-1 only).  Lean:
+# outputs only, stacked over the pairs; written by `python -m oracle.gen_golden --batch`.
+BATCH_CASES = {
+    "batch_3dmatch_n5000_l12": ("3dmatch", 5000, 12, list(range(0, 16)), 99),
+    "batch_kitti_n10000_l12": ("kitti", 10000, 12, list(range(100, 116)), 99),
+}
+
+
+def main_batch(only=None):
+    torch.set_num_threads(os.cpu_count())
+    for name, (fam, N, L, pair_seeds, w_seed) in BATCH_CASES.items():
+        if only and only not in name:
+            continue
+        cfg = synth.CONFIGS[fam]
+        sd = synth.make_state_dict(w_seed, num_layers=L, sigma_d=cfg["sigma_d"])
+        ctor = dict(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"])
+        model = ref_harness.build_reference_model(sd, **ctor)
+        cols = {k: [] for k in ("confidence", "seeds", "inlier_count", "initial_trans", "final_labels", "final_trans",
+                                "refine_sizes", "power_iters", "best_idx")}
+        for ps in pair_seeds:
+            pair = synth.make_pair(ps, N, **cfg)
+            rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
+            counts = torch.round(rec["seed_fitness"] * N).to(torch.int32)
+            sizes = rec["refine_sizes"] + [-1] * (20 - len(rec["refine_sizes"]))
+            cols["confidence"].append(rec["confidence"][0])
+            cols["seeds"].append(rec["seeds"][0].to(torch.int32))
+            cols["inlier_count"].append(counts[0])
+            cols["best_idx"].append(torch.argmax(rec["seed_fitness"][0]).to(torch.int32))
+            cols["initial_trans"].append(rec["initial_trans"][0])
+            cols["final_labels"].append(rec["final_labels"][0].to(torch.uint8))
+            cols["final_trans"].append(rec["final_trans"][0])
+            cols["refine_sizes"].append(torch.tensor(sizes, dtype=torch.int32))
+            cols["power_iters"].append(torch.tensor(rec["power_iters"], dtype=torch.int32))
+            print(name, "pair seed", ps, "labels", int(rec["final_labels"].sum()), "power iters", rec["power_iters"],
+                  "refine", rec["refine_sizes"], flush=True)
+        arrays = {k: torch.stack(v) for k, v in cols.items()}
+        meta = dict(case=name, family=fam, N=N, num_layers=L, pair_seeds=pair_seeds, weight_seed=w_seed, ctor=ctor,
+                    torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing), one pair at a time")
+        path = os.path.join(GOLDEN_DIR, name + ".npz")
+        np.savez_compressed(path, meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8),
+                            **{k_: v.numpy() for k_, v in arrays.items()})
+        print(name, os.path.getsize(path) // 1024, "KiB", flush=True)
+
+
 if __name__ == "__main__":
     import sys
-    main_full() if "--full" in sys.argv else main()
+    flags = [a for a in sys.argv[1:] if a.startswith("--")]
+    only = next((a for a in sys.argv[1:] if not a.startswith("--")), None)       # substring filter on the case names
+    if "--batch" in flags:
+        main_batch(only)
+    elif "--full" in flags:
+        main_full(only)
+    else:
+        main(only)

@@ -62,8 +62,22 @@ def run_reference(model, corr_pos, src, tgt):
 
     def eig(M, method="power"):
         rec["local_M"] = M.clone()
-        v = orig_eig(M, method)
+        # the loop (models/PointDSC.py:351-356) calls torch.allclose exactly once per iteration it runs: counting those calls
+        # records the integer side effect "iterations used" without touching the reference
+        orig_allclose = torch.allclose
+        calls = []
+
+        def counting_allclose(*a, **kw):
+            calls.append(1)
+            return orig_allclose(*a, **kw)
+
+        torch.allclose = counting_allclose
+        try:
+            v = orig_eig(M, method)
+        finally:
+            torch.allclose = orig_allclose
         rec["eigvec"] = v.clone()
+        rec["power_iters"] = len(calls)
         return v
 
     def knn(x, k, ignore_self=False, normalized=True):

@@ -3,20 +3,23 @@ oracle, plus size-independent properties at BASELINE.json's full sizes."""
 import pytest
 import torch
 
-from conftest import FULL_CASES, GOLDEN_CASES, load_golden
+from conftest import BATCH_CASES, FULL_CASES, GOLDEN_CASES, load_golden
 from oracle import restate, synth
-from parity import CONF_TOL, assert_labels_match, assert_trans_close, golden_model
+from parity import (CONF_TOL, assert_labels_match, assert_trans_close, batch_parity_report, golden_model, seed_list_report,
+                    write_report)
 
 pytestmark = pytest.mark.gpu
 
 # (attention precision mode, 1x1-conv GEMM mode)
-MODES = ["fp32", "split16", "split16+mlp16"]
+# "production" = what PointDSC() runs by default: fused tcgen05 layer path (pdsc_mlp_chain / pdsc_qkv_pack / packed attention)
+MODES = ["production", "fp32", "split16", "split16+mlp16"]
 
 
 def _mode(name):
     """-> kwargs for golden_model"""
     from pointdsc_b200 import _cabi
-    return {"fp32": dict(attn_mode=_cabi.ATTN_FP32, mlp_mode="fp32"),
+    return {"production": dict(),
+            "fp32": dict(attn_mode=_cabi.ATTN_FP32, mlp_mode="fp32"),
             "split16": dict(attn_mode=_cabi.ATTN_SPLIT16, mlp_mode="fp32"),
             "split16+mlp16": dict(attn_mode=_cabi.ATTN_SPLIT16, mlp_mode="split16")}[name]
 
@@ -41,9 +44,18 @@ def test_forward_vs_reference_golden(case, mode):
     thr = meta["ctor"]["inlier_threshold"]
     assert_labels_match(res["final_labels"][0], g["final_labels"][0], res["initial_trans"][0], g["src_keypts"][0],
                         g["tgt_keypts"][0], thr)
-    # seeds: identical wherever the reference's order is well defined and scores are separated
-    same = (res["seeds"].cpu() == g["seeds"]).float().mean().item()
-    print(f"{case}/{mode}: {100 * same:.1f}% of seed slots identical")
+    # seeds: bit-exact apart from logged near-ties (parity.seed_list_report).  The rule needs a well-defined reference
+    # order: with negative confidences the reference sorts its zero keys (non-maxima) in argsort's unspecified tie order
+    # (SURVEY 7.3-3), so those cases are logged only.
+    tol = 2 * max(dconf, 1e-7)
+    rep = seed_list_report(res["seeds"][0], g["seeds"][0], g["confidence"][0], g["src_keypts"][0],
+                           meta["ctor"]["nms_radius"], tol)
+    print(f"[tie] {case}/{mode}: seeds {rep}")
+    if float(g["confidence"].min()) > 0:
+        assert rep["unexplained"] == 0, rep
+    if mode == "production":
+        write_report(f"parity_small_{case}.json", dict(case=case, mode=mode, max_abs_dconf=dconf, rot_err_deg=re, trans_err_m=te,
+                                                        seeds=rep))
 
 
 @pytest.mark.parametrize("mode", ["production", "fp32"])
@@ -72,14 +84,15 @@ def test_forward_vs_reference_golden_at_full_size(case, mode):
     same = (res["seeds"].cpu().to(torch.int32) == g["seeds"]).float().mean().item()
     cnt_same = (res["inlier_count"].cpu() == g["inlier_count"]).float().mean().item()
     print(f"{case}/{mode}: {100 * same:.1f}% of seed slots and {100 * cnt_same:.1f}% of per-seed inlier counts identical")
-    # where a seed slot differs, the two candidates' reference scores must be closer than the confidence tolerance allows
-    # (an order decided by the last bits of the score): logged as ties, anything else is a failure
-    gs, rs = res["seeds"][0].cpu().long(), g["seeds"][0].long()
-    gap = (g["confidence"][0][gs] - g["confidence"][0][rs]).abs()
-    assert float(gap.max()) <= 2 * CONF_TOL * max(1.0, g["confidence"].abs().max().item()), float(gap.max())
-    overlap = len(set(gs.tolist()) & set(rs.tolist())) / len(rs)
-    print(f"[tie] {case}/{mode}: seed sets overlap {100 * overlap:.1f}%, largest score gap at a differing slot {float(gap.max()):.2e}")
-    assert overlap >= 0.95
+    # seeds: bit-exact apart from logged near-ties (parity.seed_list_report)
+    rep = seed_list_report(res["seeds"][0], g["seeds"][0].long(), g["confidence"][0], pair["src_keypts"][0],
+                           meta["ctor"]["nms_radius"], 2 * max(dconf, 1e-7))
+    print(f"[tie] {case}/{mode}: seeds {rep}")
+    assert rep["unexplained"] == 0, rep
+    write_report(f"parity_full_{case}_{mode}.json", dict(case=case, mode=mode, max_abs_dconf=dconf,
+                                                          dconf_vs_float64_reference=dict(ours=ours64, fp32_reference=ref64),
+                                                          rot_err_deg=re, trans_err_m=te, seeds=rep,
+                                                          inlier_count_slots_identical=cnt_same))
     if same == 1.0:
         from parity import assert_counts_match
         assert_counts_match(res["inlier_count"][0], g["inlier_count"][0], g["seed_trans"][0], pair["src_keypts"][0],
@@ -102,6 +115,29 @@ def test_batched_forward_equals_per_pair_runs():
         assert torch.equal(one["seeds"][0], res["seeds"][b])
     # pair 0 of the batch is the golden pair
     assert_trans_close(res["final_trans"][0:1], g["final_trans"])
+
+
+@pytest.mark.parametrize("case", BATCH_CASES)
+def test_production_batch_vs_reference_golden_all_pairs(case):
+    """BASELINE configs[1] (16 pairs x N=5000, pair seeds 0..15) and configs[2] (16 pairs x N=10000, seeds 100..115) as ONE
+    batch of 16 through the default path -- exactly what bench.py times -- with EVERY pair compared against the outputs of the
+    unmodified reference (tests/golden/batch_*.npz, oracle/gen_golden.py --batch).  The observed maxima and the tie counts
+    are written to gpurun_out/parity_report_<case>.json (committed as profiles/r02_parity_report_*.json)."""
+    meta, g = load_golden(case)
+    fam = synth.CONFIGS[meta["family"]]
+    N, thr = meta["N"], fam["inlier_threshold"]
+    model, _ = golden_model(meta)
+    batch = synth.make_batch(meta["pair_seeds"], N, **fam)
+    data = {k: batch[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    res = model(data)
+    torch.cuda.synchronize()
+    report = batch_parity_report(case, meta, g, batch, res, fam)
+    write_report(f"parity_report_{case}.json", report)
+    print(f"[parity] {case}: max dconf {report['max_abs_dconf']:.3e}, rot {report['max_rot_err_deg']:.2e} deg, "
+          f"trans {report['max_trans_err_m']:.2e} m, identical seed lists {report['pairs_with_identical_seed_lists']}/16, "
+          f"ties: membership {report['seed_membership_ties']} order {report['seed_order_ties']} labels {report['label_threshold_ties']}")
+    assert not report["failures"], report["failures"]
 
 
 @pytest.mark.parametrize("mode", MODES)

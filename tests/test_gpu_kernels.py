@@ -20,7 +20,7 @@ SMALL = [c for c in GOLDEN_CASES if "n2000" not in c]
 def oracle_run(case):
     meta, g = load_golden(case)
     fam = synth.CONFIGS[meta["family"]]
-    sd = synth.make_state_dict(meta["weight_seed"], num_layers=meta["num_layers"], sigma_d=fam["sigma_d"])
+    sd = synth.state_dict_for(meta, fam["sigma_d"])
     ctor = meta["ctor"]
     out = restate.forward_pair(sd, g["corr_pos"], g["src_keypts"], g["tgt_keypts"], num_layers=ctor["num_layers"],
                                inlier_threshold=ctor["inlier_threshold"], nms_radius=ctor["nms_radius"], taps=True)
@@ -279,10 +279,28 @@ def test_seed_hypotheses_vs_reference_golden(case):
     dP = moved.norm(dim=1).max(dim=-1)[0]
     scale = float(g["src_keypts"].abs().max())
     bad = (dR > 0.01) | (dP > 2e-4 * max(1.0, scale))
-    # ill-conditioned seeds (two weak singular values) are LAPACK-convention dependent: log, bound
-    print(f"seed_hypotheses: {int(bad.sum())} / {bad.numel()} seeds outside tolerance; max dR {float(dR.max()):.2e} deg")
-    assert int(bad.sum()) <= max(1, bad.numel() // 50)
-    assert int(iters[0]) == 10 or int(iters[0]) >= 1
+    # A seed may miss the tolerance only if its Kabsch problem is ill-conditioned: the rotation of a weighted covariance H
+    # with singular values s0 >= s1 >= s2 moves by ~ |dH| / (s1 + s2), so fp32 rounding (|dH| ~ 1e-6 s0) exceeds 0.01 deg once
+    # (s1 + s2) / s0 drops below ~6e-3 (a nearly collinear neighbourhood; the result then depends on the SVD routine's
+    # conventions).  Those seeds are listed; every seed with (s1 + s2) / s0 >= ILL_COND must be inside the tolerance.
+    ILL_COND = 2e-2
+    knn = g["knn_idx"][0]                                             # [S,k]
+    A = g["src_keypts"][0][knn].double()                              # [S,k,3]
+    Bp = g["tgt_keypts"][0][knn].double()
+    wr = ref_w.double()
+    wn = wr / (wr.sum(-1, keepdim=True) + 1e-6)
+    cA = (wn[:, :, None] * A).sum(1, keepdim=True)
+    cB = (wn[:, :, None] * Bp).sum(1, keepdim=True)
+    H = torch.einsum("skI,sk,skJ->sIJ", A - cA, wr, Bp - cB)
+    sv = torch.linalg.svdvals(H)
+    ratio = (sv[:, 1] + sv[:, 2]) / sv[:, 0].clamp_min(1e-300)
+    ill = torch.nonzero(bad).flatten().tolist()
+    print(f"[ill-conditioned] seed_hypotheses {case}: {len(ill)} / {bad.numel()} seeds outside tolerance: "
+          + ", ".join(f"seed {s_} (s1+s2)/s0={float(ratio[s_]):.1e} dR={float(dR[s_]):.1e}deg" for s_ in ill[:12])
+          + f"; max dR over well-conditioned seeds {float(dR[ratio >= ILL_COND].max()):.2e} deg")
+    assert all(float(ratio[s_]) < ILL_COND for s_ in ill), [(s_, float(ratio[s_])) for s_ in ill]
+    # iterations used: the reference's own count (oracle/ref_harness.py wraps the loop of models/PointDSC.py:351-356)
+    assert int(iters[0]) == int(g["power_iters"][0])
 
 
 def test_seed_hypotheses_early_stop_rule():

@@ -79,7 +79,7 @@ def test_cpu_tensors_are_refused():
 def test_host_mlps_match_oracle(case, monkeypatch):
     meta, g = load_golden(case)
     fam = synth.CONFIGS[meta["family"]]
-    sd = synth.make_state_dict(meta["weight_seed"], num_layers=meta["num_layers"], sigma_d=fam["sigma_d"])
+    sd = synth.state_dict_for(meta, fam["sigma_d"])
     m = PointDSC(**meta["ctor"]).eval()
     m.load_state_dict(sd)
 
