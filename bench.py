@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--pairs", type=int, default=16, help="pairs per step per GPU")
     ap.add_argument("--n", type=int, default=5000, help="correspondences per pair")
     ap.add_argument("--family", default="3dmatch", choices=["3dmatch", "kitti"])
-    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "split16x3", "fp16"])
+    ap.add_argument("--mode", default=os.environ.get("POINTDSC_ATTN_MODE", "split16"), choices=["fp32", "split16", "split16pv2", "fp16"])
     ap.add_argument("--cpu-pairs", type=int, default=3, help="pairs in the cpu_baseline sample (first is warm-up)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--weight-seed", type=int, default=99, help="seed of the synthetic weights (oracle/synth.py)")
@@ -268,7 +268,7 @@ def main():
                      nms_radius=cfg["nms_radius"]).eval()
     model.load_state_dict(sd, strict=True)
     model = model.to(dev)
-    model.attn_mode = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16x3": _cabi.ATTN_SPLIT16X3,
+    model.attn_mode = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16pv2": _cabi.ATTN_SPLIT16_PV2,
                        "fp16": _cabi.ATTN_FP16}[args.mode]
 
     keys = ("corr_pos", "src_keypts", "tgt_keypts")
@@ -370,7 +370,7 @@ def main():
         torch.cuda.current_stream().synchronize()      # the caller reads the result
         return r
 
-    for _ in range(max(1, args.warmup // 2)):
+    for _ in range(args.warmup):
         step_e2e()
     barrier()
     e2e_ms, _, _, e2e_step_stats, _ = timed_region(step_e2e)
@@ -390,16 +390,15 @@ def main():
         flops_per_launch = 4.0 * args.n * args.n * C * args.pairs          # QK^T + PV, per layer, per batch
         avg_attn_ms = sum(attn_ms) / max(1, len(attn_ms))
         achieved = flops_per_launch / (avg_attn_ms * 1e-3) / 1e12
-        terms = {"fp16": 1.0, "split16": 2.5, "split16x3": 3.0, "fp32": 0.0}[args.mode]
+        terms = {"fp16": 1.0, "split16": 3.0, "split16pv2": 2.5, "fp32": 0.0}[args.mode]
         roofline = {"bound": "tensor", "kernel": f"pdsc_{attn_name}[{args.mode}]", "achieved": achieved,
                     "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_sustained"],
                     "traffic": ncu_traffic(args), "traffic_source": f"committed capture {NCU_ATTN_PROFILE} (ncu --set full of this kernel on "
                     "this workload; not measured by this run); algorithmic HBM bytes per launch = 4*B*N*C*4", "peak_source": pk["source"] + ", bf16 sustained",
                     "algorithmic_flops_per_launch": flops_per_launch, "avg_launch_ms": avg_attn_ms,
                     "launches_timed": len(attn_ms), "share_of_step": sum(attn_ms) / dev_ms,
-                    # fp32-grade results from fp16 tensor-core products: Q K^T as hi*hi + hi*lo + lo*hi (3 terms), P V as
-                    # P_hi*(V_hi + V_lo) (2 terms; 3 in split16x3): the tensor pipe does `mma_terms_avg` x the algorithmic
-                    # work, so `frac` cannot exceed 1 / mma_terms_avg
+                    # fp32-grade results from fp16 tensor-core products: each contraction as hi*hi + hi*lo + lo*hi (3 terms):
+                    # the tensor pipe does `mma_terms_avg` x the algorithmic work, so `frac` cannot exceed 1 / mma_terms_avg
                     "mma_terms_avg": terms, "issued": achieved * terms if terms else None,
                     "issued_frac": achieved * terms / pk["bf16_sustained"] if terms else None}
         line = {

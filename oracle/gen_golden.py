@@ -138,7 +138,12 @@ def main_batch(only=None):
         ctor = dict(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"])
         model = ref_harness.build_reference_model(sd, **ctor)
         cols = {k: [] for k in ("confidence", "seeds", "inlier_count", "initial_trans", "final_labels", "final_trans",
-                                "refine_sizes", "power_iters", "best_idx")}
+                                "refine_sizes", "power_iters", "best_idx", "confidence_f64", "final_trans_f64")}
+        torch.set_default_dtype(torch.float64)
+        try:
+            model64 = ref_harness.build_reference_model(sd, **ctor).double()
+        finally:
+            torch.set_default_dtype(torch.float32)
         for ps in pair_seeds:
             pair = synth.make_pair(ps, N, **cfg)
             rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
@@ -153,6 +158,17 @@ def main_batch(only=None):
             cols["final_trans"].append(rec["final_trans"][0])
             cols["refine_sizes"].append(torch.tensor(sizes, dtype=torch.int32))
             cols["power_iters"].append(torch.tensor(rec["power_iters"], dtype=torch.int32))
+            # the same unmodified reference in float64: this pair's fp32 noise floor (how far the reference's own fp32 result
+            # is from exact arithmetic)
+            torch.set_default_dtype(torch.float64)
+            try:
+                rec64 = ref_harness.run_reference(model64, pair["corr_pos"].double(), pair["src_keypts"].double(),
+                                                  pair["tgt_keypts"].double())
+            finally:
+                torch.set_default_dtype(torch.float32)
+            cols["confidence_f64"].append(rec64["confidence"][0])
+            cols["final_trans_f64"].append(rec64["final_trans"][0])
+            print("   fp32 reference vs float64 reference: max |dconf|", float((rec["confidence"][0].double() - rec64["confidence"][0]).abs().max()), flush=True)
             print(name, "pair seed", ps, "labels", int(rec["final_labels"].sum()), "power iters", rec["power_iters"],
                   "refine", rec["refine_sizes"], flush=True)
         arrays = {k: torch.stack(v) for k, v in cols.items()}

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200.so")
 # (tests and scripts/ select it with use_tuning_library(); the product path never loads it)
 TUNING_LIB_PATH = os.path.join(_HERE, "lib", "libpointdsc_b200_tuning.so")
 
-ATTN_FP32, ATTN_SPLIT16, ATTN_FP16, ATTN_SPLIT16X3 = 0, 1, 2, 3
+ATTN_FP32, ATTN_SPLIT16, ATTN_FP16, ATTN_SPLIT16_PV2 = 0, 1, 2, 3
 OP_NONLOCAL_ATTN, OP_PICK_SEEDS, OP_SEED_KNN, OP_SEED_HYPOTHESES = 1, 2, 3, 4
 OP_SCORE_HYPOTHESES, OP_POST_REFINE, OP_POWER_ITER_FULL = 5, 6, 7
 OP_HYBRID_SEARCH, OP_VOXEL_DOWN_SAMPLE, OP_NN_MATCH_F64, OP_ICP_REFINE = 8, 9, 10, 11

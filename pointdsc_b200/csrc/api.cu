@@ -110,7 +110,7 @@ int pdsc_nonlocal_attn(const float* q, const float* k, const float* v, int64_t l
     PDSC_REQUIRE(sigma_spat > 0.f, "nonlocal_attn: sigma_spat must be positive");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (mode == PDSC_ATTN_FP32) return launch_attn_fp32(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, st);
-    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16X3)
+    if (mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16_PV2)
         return launch_attn_pp(q, k, v, ld_qkv, src, tgt, out, ld_out, B, N, C, sigma_spat, mode, ws, ws_bytes, st);
     set_error("nonlocal_attn: unknown precision mode %d", mode);
     return PDSC_ERR_ARG;
@@ -130,8 +130,8 @@ int pdsc_nonlocal_attn_packed(float* out, int64_t ld_out, int B, int N, int C, i
     PDSC_REQUIRE(out && ws, "nonlocal_attn_packed: null pointer");
     PDSC_REQUIRE(B > 0 && N > 0, "nonlocal_attn_packed: bad shape B=%d N=%d", B, N);
     PDSC_REQUIRE(ld_out >= C && ld_out % 4 == 0 && aligned16(out), "nonlocal_attn_packed: bad output stride/alignment");
-    PDSC_REQUIRE(mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16X3,
-                 "nonlocal_attn_packed: mode must be SPLIT16, SPLIT16X3 or FP16");
+    PDSC_REQUIRE(mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_FP16 || mode == PDSC_ATTN_SPLIT16_PV2,
+                 "nonlocal_attn_packed: mode must be SPLIT16, SPLIT16_PV2 or FP16");
     return launch_attn_pp_main(out, ld_out, B, N, C, mode, ws, ws_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -7,13 +7,11 @@
 //   msg = W V                      tcgen05.mma with P read from TMEM (aliasing S) and V^T from smem
 //
 // Precision: every fp32 operand x is split into fp16 hi + fp16 lo (22 mantissa bits), fp32 accumulation.
-//   PDSC_ATTN_SPLIT16X3  both contractions as hi*hi + hi*lo + lo*hi (3 MMAs per k-step).
-//   PDSC_ATTN_SPLIT16    (default) Q K^T with all three terms; P V as P_hi V_hi + P_hi V_lo.  The reference maximum of the
-//                        online softmax is kept an INTEGER (log2 units), so the weight of every key with compat = 0 -- the
-//                        great majority: logit exactly 0, weight exp2(-m) -- is a power of two and exact in fp16; the
-//                        remaining weights carry independent fp16 rounding errors, and because the row sum is taken over
-//                        the SAME rounded weights they only perturb a softmax that is then re-normalised (no P_lo term
-//                        needed: as accurate as X3 in scripts/precision_study.py and in the parity reports).
+//   PDSC_ATTN_SPLIT16      (default) both contractions as hi*hi + hi*lo + lo*hi (3 MMAs per k-step).
+//   PDSC_ATTN_SPLIT16_PV2  P V without the P_lo V_hi term, the row sum taken over the rounded P_hi.  Measured in round 2:
+//                          the rounding of P (2^-12 relative, independent per key) acts like a 7e-4 perturbation of the
+//                          logits; 2e-4 message error on random inputs and 3e-4 in the 12-layer confidences of the
+//                          KITTI-shaped batch -- outside the tolerance -- for 6 % of the launch time.  Not the default.
 //   PDSC_ATTN_FP16       hi*hi only.
 //
 // One CTA works on 256 query rows of one pair as two 128-row sub-tiles X = A, B that alternate on
@@ -373,7 +371,7 @@ __device__ __forceinline__ float4 pp_ldcg4(const float* p) {
 // 256-row blocks; each loads HALF of every K / V^T tile and multicasts it to both (cp.async.bulk .multicast::cluster),
 // which halves the L2 -> SM traffic; a stage is released by both MMA issuers (multicast tcgen05.commit).
 // DBG: instantiation with the timing-experiment knobs (PDSC_ATTN_DBG) and the timeline trace compiled in.
-// PV3: the P_lo V_hi term is issued (PDSC_ATTN_SPLIT16X3), so the softmax threads also store the fp16 remainder of P.
+// PV3: the P_lo V_hi term is issued (PDSC_ATTN_SPLIT16), so the softmax threads also store the fp16 remainder of P.
 template <int CL, bool DBG, bool CHAIN = false, bool PV3 = false>
 __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p) {
     constexpr int NP = 16;                   // key pairs per thread per tile (32 keys)
@@ -939,9 +937,9 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     p.NU = CL == 1 ? NRB : NRBp / 2;
     p.total_steps = (long long)B * p.NU * NT;
     // hi/lo product terms per contraction (see the precision note at the top of the file)
-    const bool split = mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_SPLIT16X3;
+    const bool split = mode == PDSC_ATTN_SPLIT16 || mode == PDSC_ATTN_SPLIT16_PV2;
     p.qk_terms = split ? (PP_QK_HH | PP_QK_HL | PP_QK_LH) : PP_QK_HH;
-    p.pv_terms = mode == PDSC_ATTN_SPLIT16X3 ? 3 : (mode == PDSC_ATTN_SPLIT16 ? 2 : 1);
+    p.pv_terms = mode == PDSC_ATTN_SPLIT16 ? 3 : (mode == PDSC_ATTN_SPLIT16_PV2 ? 2 : 1);
     if (split) {   // PDSC_ATTN_QK_TERMS (bit mask) / PDSC_ATTN_PV_TERMS (1..3): tuning build only
         const int qk = tuning_int("PDSC_ATTN_QK_TERMS", -1), pv = tuning_int("PDSC_ATTN_PV_TERMS", -1);
         if (qk >= 1 && qk <= 7 && (qk & 1)) p.qk_terms = qk;

@@ -27,8 +27,11 @@ int num_sms();
 
 // Opt-in to more than 48 KB of dynamic shared memory.  The attribute is per device (and per function), so the cache is
 // keyed by the current device: a process that runs on cuda:0 and then on cuda:1 opts in on both.
+// (`static`: internal linkage.  An inline template's local static is a GNU-unique symbol, ONE object per process even across
+// dlopen(RTLD_LOCAL), so the product and the tuning library -- both loaded by the tests -- would share the cache while each
+// has its own kernels.)
 template <auto Kernel>
-inline void opt_in_smem(int bytes) {
+static void opt_in_smem(int bytes) {
     static thread_local int set_bytes[64];      // zero-initialised; per kernel instantiation
     int dev = 0;
     cudaGetDevice(&dev);

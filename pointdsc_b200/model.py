@@ -27,7 +27,7 @@ import torch.nn.functional as F
 
 from . import _cabi
 
-_MODE_NAMES = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16x3": _cabi.ATTN_SPLIT16X3,
+_MODE_NAMES = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16pv2": _cabi.ATTN_SPLIT16_PV2,
                "fp16": _cabi.ATTN_FP16}
 _MLP_MODES = ("fused", "split16", "fp32")
 

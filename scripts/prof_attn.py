@@ -3,7 +3,7 @@ import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from pointdsc_b200 import _cabi
-mode = {"fp32": 0, "split16": 1, "fp16": 2, "split16x3": 3}[sys.argv[1] if len(sys.argv) > 1 else "split16"]
+mode = {"fp32": 0, "split16": 1, "fp16": 2, "split16pv2": 3}[sys.argv[1] if len(sys.argv) > 1 else "split16"]
 if any(k.startswith("PDSC_") for k in os.environ):      # knobs only exist in the -DPDSC_TUNING build
     _cabi.use_tuning_library().__enter__()
     print("tuning library:", {k: v for k, v in os.environ.items() if k.startswith("PDSC_")})

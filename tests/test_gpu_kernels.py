@@ -389,16 +389,16 @@ def _attn_ref(qkv, src, tgt, sigma):
     return torch.cat(outs)
 
 
-@pytest.mark.parametrize("mode", ["split16", "split16x3"])
+@pytest.mark.parametrize("mode", ["split16", "split16pv2"])
 @pytest.mark.parametrize("grid", [None, "0", "5", "7"])
 @pytest.mark.parametrize("N", [128, 1, 100, 129, 256, 257, 700, 1100])
 def test_attention_split16_vs_oracle(N, grid, mode, monkeypatch, tuning_lib):
     """grid: None = stream-K over all SMs (partials + last-arriver combine), "0" = one CTA per 256-row
-    block (no partials), "5"/"7" = a few CTAs whose ranges cut blocks at odd places.  mode: the default term set
-    (P_hi only, integer reference maximum) and the three-term form."""
+    block (no partials), "5"/"7" = a few CTAs whose ranges cut blocks at odd places.  mode: the default three-term form,
+    and the form without P_lo (measurement mode: ~2^-12 relative message error, so a looser bound)."""
     from pointdsc_b200 import _cabi
-    if mode == "split16x3" and grid in ("0", "7"):
-        pytest.skip("three-term form: stream-K and one odd grid are enough")
+    if mode == "split16pv2" and grid in ("0", "7"):
+        pytest.skip("P_lo-free form: stream-K and one odd grid are enough")
     if grid is None:
         monkeypatch.delenv("PDSC_ATTN_GRID", raising=False)
     else:
@@ -410,12 +410,12 @@ def test_attention_split16_vs_oracle(N, grid, mode, monkeypatch, tuning_lib):
     tgt = src + 0.05 * torch.randn(B, N, 3, generator=g)
     d = cu(qkv)
     out = _cabi.nonlocal_attn(d[:, :, :C], d[:, :, C:2 * C], d[:, :, 2 * C:], cu(src), cu(tgt), 0.1,
-                              mode=_cabi.ATTN_SPLIT16 if mode == "split16" else _cabi.ATTN_SPLIT16X3)
+                              mode=_cabi.ATTN_SPLIT16 if mode == "split16" else _cabi.ATTN_SPLIT16_PV2)
     torch.cuda.synchronize()
     ref = _attn_ref(qkv, src, tgt, 0.1)
     err = (out.cpu() - ref).abs().max().item()
     print(f"{mode} attention N={N} grid={grid}: max abs err {err:.3e}")
-    assert err < 5e-5
+    assert err < (5e-5 if mode == "split16" else 1e-3)
 
 
 @pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation", "chain3", "chain1"])
