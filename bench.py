@@ -245,6 +245,74 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------
+def config4_leg(n, dist, dev, rank, world, reps=5, warm=2):
+    """BASELINE configs[3]: ONE pair with N=50000 correspondences, the full-matrix power iteration
+    (cal_leading_eigenvector, models/PointDSC.py:338-358, on the N x N compatibility matrix) with the rows sharded over the
+    ranks.  Transport of the eigenvector: direct NVLink stores + device-side arrival flags (parallel.power_iteration_full_p2p)
+    and, beside it, one NCCL all-gather per iteration (parallel.power_iteration_full_sharded).  Times are CUDA events around
+    `reps` back-to-back runs, max over ranks; rank 0 also runs the single-GPU driver and compares bit for bit."""
+    from oracle import synth
+    from pointdsc_b200 import _cabi, parallel
+    cfg = synth.CONFIGS["kitti"]
+    pair = synth.make_pair(200, n, **cfg)
+    src, tgt = pair["src_keypts"][0].to(dev).contiguous(), pair["tgt_keypts"][0].to(dev).contiguous()
+    sig, iters_max = cfg["sigma_d"], 10
+
+    def timed(fn):
+        for _ in range(warm):
+            out = fn()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), out
+
+    leg = {"workload": f"single pair N={n} (KITTI-shaped, seed 200), full-matrix power iteration, {iters_max} iterations max, "
+                       f"rows sharded over {world} GPU(s)", "N": n, "n_gpus": world, "reps": reps,
+           "exchange_bytes_per_iteration": 4 * n if world > 1 else 0}
+    if world == 1:
+        ms, (v, it) = timed(lambda: _cabi.power_iter_full(src, tgt, sig, iters_max))
+        leg.update(transport="none (one GPU)", ms=ms, iterations=int(it[0]), bit_identical_to_1gpu=True)
+    else:
+        ag_ms, (v_ag, it_ag) = timed(lambda: parallel.power_iteration_full_sharded(src, tgt, sig, iters_max))
+        leg["allgather_ms"] = ag_ms
+        v, it, ms, transport = v_ag, it_ag, ag_ms, "nccl all-gather per iteration"
+        ok = torch.ones(1, device=dev)
+        try:
+            ex = parallel.PeerExchange(n, dev)
+        except Exception as e:      # no peer mappings on this box: the all-gather transport is what ran
+            ok.zero_()
+            leg["p2p_unavailable"] = f"{type(e).__name__}: {e}"[:300]
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() > 0:
+            ms, (v, it) = timed(lambda: parallel.power_iteration_full_p2p(src, tgt, sig, iters_max, ex))
+            transport = "nvlink p2p stores from the matvec epilogue + device-side arrival flags (no collective)"
+            leg["allgather_equals_p2p"] = bool(torch.equal(v, v_ag))
+        leg.update(transport=transport, ms=ms, iterations=int(it[0]))
+        if rank == 0:
+            one_ms, (v1, it1) = None, _cabi.power_iter_full(src, tgt, sig, iters_max)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            v1, it1 = _cabi.power_iter_full(src, tgt, sig, iters_max)
+            e1.record()
+            torch.cuda.synchronize()
+            leg.update(single_gpu_ms_same_box=e0.elapsed_time(e1), bit_identical_to_1gpu=bool(torch.equal(v, v1)) and int(it[0]) == int(it1[0]))
+        dist.barrier()
+    leg["effective_GBps_4N2_per_iteration"] = 4.0 * n * n * leg["iterations"] / (leg["ms"] * 1e-3) / 1e9
+    return leg
+
+
+# ------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -385,6 +453,11 @@ def main():
     value = total_pairs / (dev_ms / 1e3)
     e2e_value = total_pairs / (e2e_ms / 1e3)
 
+    # -------- config 4 leg: row-sharded power iteration of one N=50000 pair (all ranks take part) ------
+    c4 = None
+    if not args.no_config4:
+        c4 = config4_leg(args.config4_n, dist, dev, rank, world)
+
     if rank == 0:
         pk = peaks()
         flops_per_launch = 4.0 * args.n * args.n * C * args.pairs          # QK^T + PV, per layer, per batch
@@ -422,6 +495,8 @@ def main():
             "roofline": roofline,
             "wall_s_timed_region": t_wall,
         }
+        if c4 is not None:
+            line["config4"] = c4
         chk = golden_check(args, res, batch, rank)
         if chk is not None:
             line["parity_check"] = chk

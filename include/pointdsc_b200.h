@@ -200,6 +200,24 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
                          float sigma_spat, int num_iterations, int32_t* iters_out,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* Row-sharded run of the same iteration over NVLink (BASELINE config 4: one pair, N >= 50k, rows split over the GPUs of
+ *  one box; cal_leading_eigenvector models/PointDSC.py:338-358).  Instead of an all-gather per iteration, the matvec kernel
+ *  of every rank stores its rows straight into the y buffer of EVERY rank (peer pointers into symmetric memory) and then
+ *  publishes a system-scope arrival flag; the normalise kernel of every rank waits on the device for all `world` flags.
+ *  Two launches per iteration, no collective, no host synchronisation; the bits equal the single-GPU run.
+ *  Exchange buffer (one per rank, pdsc_power_p2p_exchange_bytes(N) bytes, zero-filled once before the first use, mapped
+ *  on every peer): y[parity 0] | y[parity 1] | flags.  peer_bases: HOST array of `world` device pointers, entry p = the
+ *  address of rank p's exchange buffer as seen from this rank.  seq: 1, 2, 3, ... one value per iteration, the same on
+ *  all ranks, strictly increasing over the life of the buffers (the y parity is seq & 1).  All ranks must enqueue the
+ *  same sequence of calls. */
+#define PDSC_P2P_MAX_WORLD 8
+size_t pdsc_power_p2p_exchange_bytes(int N);
+int pdsc_compat_matvec_p2p(const float* src, const float* tgt, const float* v, int N, int row_begin, int row_end,
+                           float sigma_spat, const int32_t* converged_flag, void* const* peer_bases,
+                           int world, int rank, int seq, void* stream);
+int pdsc_power_normalize_p2p(void* exchange_base, float* v_inout, int N, int32_t* converged_flag,
+                             int32_t* iters_done, int world, int seq, void* stream);
+
 /* ---- next rows: the callers either side of the forward -------------------------------------------- */
 
 /* (N2) nearest neighbour in descriptor space; replaces find_nn algorithms/matching.py:22-65 and the

@@ -128,7 +128,9 @@ BATCH_CASES = {
 }
 
 
-def main_batch(only=None):
+def main_batch(only=None, reuse_f64=False):
+    """reuse_f64: keep the float64 columns of the existing fixture (they come from this same function; the float64 pass is
+    the slow part) and redo the fp32 pass only."""
     torch.set_num_threads(os.cpu_count())
     for name, (fam, N, L, pair_seeds, w_seed) in BATCH_CASES.items():
         if only and only not in name:
@@ -138,16 +140,23 @@ def main_batch(only=None):
         ctor = dict(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"])
         model = ref_harness.build_reference_model(sd, **ctor)
         cols = {k: [] for k in ("confidence", "seeds", "inlier_count", "initial_trans", "final_labels", "final_trans",
-                                "refine_sizes", "power_iters", "best_idx", "confidence_f64", "final_trans_f64")}
+                                "refine_sizes", "power_iters", "best_idx", "best_knn_idx", "confidence_f64", "final_trans_f64")}
+        old = None
+        if reuse_f64 and os.path.exists(os.path.join(GOLDEN_DIR, name + ".npz")):
+            old = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+            old = old if "confidence_f64" in old.files else None
         torch.set_default_dtype(torch.float64)
         try:
             model64 = ref_harness.build_reference_model(sd, **ctor).double()
         finally:
             torch.set_default_dtype(torch.float32)
-        for ps in pair_seeds:
+        for pi, ps in enumerate(pair_seeds):
             pair = synth.make_pair(ps, N, **cfg)
             rec = ref_harness.run_reference(model, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"])
             counts = torch.round(rec["seed_fitness"] * N).to(torch.int32)
+            # the neighbour list of the winning seed (models/PointDSC.py:251-252): where a near-tie in feature distance gives
+            # another list, the tests re-run that one hypothesis on the reference's list (tests/parity.py)
+            cols["best_knn_idx"].append(rec["knn_idx"][0, int(torch.argmax(rec["seed_fitness"][0]))].to(torch.int32))
             sizes = rec["refine_sizes"] + [-1] * (20 - len(rec["refine_sizes"]))
             cols["confidence"].append(rec["confidence"][0])
             cols["seeds"].append(rec["seeds"][0].to(torch.int32))
@@ -160,6 +169,10 @@ def main_batch(only=None):
             cols["power_iters"].append(torch.tensor(rec["power_iters"], dtype=torch.int32))
             # the same unmodified reference in float64: this pair's fp32 noise floor (how far the reference's own fp32 result
             # is from exact arithmetic)
+            if old is not None:
+                cols["confidence_f64"].append(torch.from_numpy(old["confidence_f64"][pi]))
+                cols["final_trans_f64"].append(torch.from_numpy(old["final_trans_f64"][pi]))
+                continue
             torch.set_default_dtype(torch.float64)
             try:
                 rec64 = ref_harness.run_reference(model64, pair["corr_pos"].double(), pair["src_keypts"].double(),
@@ -185,7 +198,7 @@ if __name__ == "__main__":
     flags = [a for a in sys.argv[1:] if a.startswith("--")]
     only = next((a for a in sys.argv[1:] if not a.startswith("--")), None)       # substring filter on the case names
     if "--batch" in flags:
-        main_batch(only)
+        main_batch(only, reuse_f64="--reuse-f64" in flags)
     elif "--full" in flags:
         main_full(only)
     else:

@@ -67,6 +67,10 @@ SIGNATURES = {
     "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_icp_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_double, c_int, c_double, c_double, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_power_p2p_exchange_bytes": (c_size_t, [c_int]),
+    "pdsc_compat_matvec_p2p": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_int, c_int,
+                                       c_int, c_void_p]),
+    "pdsc_power_normalize_p2p": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
                                      c_void_p, c_size_t, c_void_p]),
 }
@@ -417,6 +421,34 @@ def power_iter_full(src, tgt, sigma_spat, num_iterations, ws=None):
     _check(rc, "pdsc_power_iter_full")
     _count()
     return v, iters
+
+
+P2P_MAX_WORLD = 8
+
+
+def power_p2p_exchange_bytes(N):
+    return int(load().pdsc_power_p2p_exchange_bytes(int(N)))
+
+
+def compat_matvec_p2p(src, tgt, v, row_begin, row_end, sigma_spat, converged_flag, peer_ptrs, rank, seq):
+    """One rank's rows of M v, stored into every rank's exchange buffer (peer_ptrs: device addresses, as ints)."""
+    lib = load()
+    world = len(peer_ptrs)
+    arr = (c_void_p * world)(*[int(p) for p in peer_ptrs])
+    rc = lib.pdsc_compat_matvec_p2p(_ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"), _ptr(v, torch.float32, "v"),
+                                    v.shape[0], int(row_begin), int(row_end), float(sigma_spat), _ptr(converged_flag),
+                                    ctypes.cast(arr, c_void_p), world, int(rank), int(seq), _stream())
+    _check(rc, "pdsc_compat_matvec_p2p")
+    _count()
+
+
+def power_normalize_p2p(exchange_ptr, v, converged_flag, iters_done, world, seq):
+    lib = load()
+    rc = lib.pdsc_power_normalize_p2p(int(exchange_ptr), _ptr(v, torch.float32, "v"), v.shape[0],
+                                      _ptr(converged_flag, torch.int32, "flag"), _ptr(iters_done), int(world), int(seq), _stream())
+    _check(rc, "pdsc_power_normalize_p2p")
+    _count()
+    return v
 
 
 MATCH_DOT, MATCH_L2 = 0, 1

@@ -266,6 +266,28 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
                            reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t pdsc_power_p2p_exchange_bytes(int N) { return N > 0 ? power_p2p_exchange_bytes(N) : 0; }
+
+int pdsc_compat_matvec_p2p(const float* src, const float* tgt, const float* v, int N, int row_begin, int row_end,
+                           float sigma_spat, const int32_t* converged_flag, void* const* peer_bases, int world, int rank, int seq,
+                           void* stream) {
+    PDSC_REQUIRE(src && tgt && v && peer_bases, "compat_matvec_p2p: null pointer");
+    PDSC_REQUIRE(N > 0 && row_begin >= 0 && row_end <= N && row_begin <= row_end, "compat_matvec_p2p: bad row range");
+    PDSC_REQUIRE(world >= 1 && world <= PDSC_P2P_MAX_WORLD && rank >= 0 && rank < world && seq > 0,
+                 "compat_matvec_p2p: bad world=%d rank=%d seq=%d (world <= %d, seq > 0)", world, rank, seq, PDSC_P2P_MAX_WORLD);
+    for (int p = 0; p < world; ++p) PDSC_REQUIRE(peer_bases[p] && aligned16(peer_bases[p]), "compat_matvec_p2p: bad peer base %d", p);
+    return launch_compat_matvec_p2p(src, tgt, v, N, row_begin, row_end, sigma_spat, converged_flag, peer_bases, world, rank, seq,
+                                    reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_power_normalize_p2p(void* exchange_base, float* v_inout, int N, int32_t* converged_flag, int32_t* iters_done, int world,
+                             int seq, void* stream) {
+    PDSC_REQUIRE(exchange_base && v_inout && converged_flag, "power_normalize_p2p: null pointer");
+    PDSC_REQUIRE(N > 0 && world >= 1 && world <= PDSC_P2P_MAX_WORLD && seq > 0, "power_normalize_p2p: bad arguments");
+    return launch_power_normalize_p2p(exchange_base, v_inout, N, converged_flag, iters_done, world, seq,
+                                      reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx_out, double* dist2_out,
                        int32_t* count_out, double* normals_out, void* ws, size_t ws_bytes, void* stream) {
     PDSC_REQUIRE(pts && ws && (idx_out || normals_out), "hybrid_search: null pointer");

@@ -260,6 +260,12 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
                      const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y,
                      void* y_packed, int Kp, cudaStream_t st);
 size_t power_workspace(int N);
+size_t power_p2p_exchange_bytes(int N);
+int launch_compat_matvec_p2p(const float* src, const float* tgt, const float* v, int N, int row_begin, int row_end,
+                             float sigma_spat, const int32_t* converged_flag, void* const* peer_bases, int world, int rank,
+                             int seq, cudaStream_t st);
+int launch_power_normalize_p2p(void* exchange_base, float* v, int N, int32_t* converged_flag, int32_t* iters_done, int world,
+                               int seq, cudaStream_t st);
 int power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
                     int32_t* iters_out, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,

@@ -148,7 +148,10 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                 const uint32_t lo_off = (uint32_t)(K / 64) * blk;         // lo image follows the hi image
                 const uint64_t wd = ml_uniform64(umma_desc_sw128_kmajor(smem_u32(wsm + p.w_off[l])));
                 uint32_t acc = 0;
-                for (int term = 0; term < 3; ++term) {
+                // cross terms first (term order 1, 2, 0 = hi*lo, lo*hi, hi*hi): the TMEM accumulator truncates once per MMA at
+                // the magnitude of the running sum, so the small terms go in while that sum is still small
+                for (int ti = 0; ti < 3; ++ti) {
+                    const int term = ti == 2 ? 0 : ti + 1;
                     const uint32_t a0 = tmem + (term == 2 ? ML_A_LO : 0u);
                     const uint32_t b0 = term == 1 ? lo_off : 0u;
                     for (int kk = 0; kk < K / 16; ++kk) {

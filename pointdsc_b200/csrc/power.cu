@@ -30,11 +30,34 @@ __device__ __forceinline__ float mv_fma_sat(float a, float b, float c) {
 // fills the machine.  Arithmetic: points are scaled by 1/sigma when a tile is staged (no division per entry), a thread
 // owns two rows as the two lanes of packed f32x2 adds / FMAs, distances by sqrt.approx (MUFU), 1 - c^2 by one saturating
 // FMA: 2 MUFU + ~9 packed FP32 instructions per pair of entries (the exact-rounding form it replaces cost ~50 per entry).
+//
+// P2P = true (row-sharded run over NVLink, config 4): rank 0 of every cluster stores its 128 results straight into the y
+// buffer of EVERY rank (peer device pointers into symmetric memory; y is indexed by the global row, so there is no
+// padding and no gather step), and the last cluster of the grid to finish (device-scope counter) publishes this rank's
+// arrival: a system-scope release store of `seq` into flag slot `rank` of every peer.  The normalise kernel of each rank
+// waits for all `world` slots to reach `seq` (power_normalize_kernel), so one iteration is two launches and no collective.
+struct MvPeers {
+    float* y[PDSC_P2P_MAX_WORLD];          // y buffer (of this iteration's parity) on every rank
+    int32_t* flags[PDSC_P2P_MAX_WORLD];    // arrival flags [world] on every rank
+    int32_t* done;                          // this rank's cluster counter
+    int world, rank, seq;
+};
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <bool P2P>
 __global__ void __cluster_dims__(1, MV_KS, 1) __launch_bounds__(MV_THREADS)
 compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tgt, const float* __restrict__ v,
                      float* __restrict__ y, int N, int row_begin, int row_end, float inv_sigma,
-                     const int32_t* __restrict__ converged_flag) {
-    if (converged_flag && *converged_flag) return;          // uniform over the grid
+                     const int32_t* __restrict__ converged_flag, const MvPeers peers) {
+    if (converged_flag && *converged_flag) return;          // uniform over the grid (and over the ranks: every rank normalises the same y)
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ float4 ta[MV_TILE];   // src xyz / sigma, v
     __shared__ float4 tb[MV_TILE];   // tgt xyz / sigma, unused
@@ -96,21 +119,56 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
         float2 c[MV_KS];
 #pragma unroll
         for (int k = 0; k < MV_KS; ++k) c[k] = cluster.map_shared_rank(csum, k)[rl];
-        if (r0 < row_end) y[r0 - row_begin] = ((c[0].x + c[1].x) + (c[2].x + c[3].x)) + ((c[4].x + c[5].x) + (c[6].x + c[7].x));
-        if (r1 < row_end) y[r1 - row_begin] = ((c[0].y + c[1].y) + (c[2].y + c[3].y)) + ((c[4].y + c[5].y) + (c[6].y + c[7].y));
+        const float y0 = ((c[0].x + c[1].x) + (c[2].x + c[3].x)) + ((c[4].x + c[5].x) + (c[6].x + c[7].x));
+        const float y1 = ((c[0].y + c[1].y) + (c[2].y + c[3].y)) + ((c[4].y + c[5].y) + (c[6].y + c[7].y));
+        if (!P2P) {
+            if (r0 < row_end) y[r0 - row_begin] = y0;
+            if (r1 < row_end) y[r1 - row_begin] = y1;
+        } else {
+            for (int p = 0; p < peers.world; ++p) {           // NVLink stores (coalesced 256-byte runs per peer)
+                if (r0 < row_end) peers.y[p][r0] = y0;
+                if (r1 < row_end) peers.y[p][r1] = y1;
+            }
+            __threadfence_system();                           // this thread's peer stores are ordered before the counter
+        }
+    }
+    if (P2P && ks == 0) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int arrived = atomicAdd(peers.done, 1);
+            if (arrived == (int)gridDim.x - 1) {              // last cluster of this rank: everything is written
+                *peers.done = 0;                              // ready for the next launch
+                __threadfence_system();
+                for (int p = 0; p < peers.world; ++p) st_release_sys(peers.flags[p] + peers.rank, peers.seq);
+            }
+        }
     }
     cluster.sync();                                           // peers keep their shared memory until rank 0 has read it
 }
 
+// wait_flags != nullptr (P2P run): y is complete once every rank's arrival flag has reached `seq`; the waiting threads poll
+// with system-scope acquire loads (bounded: a lost peer traps instead of hanging the GPU), the barrier orders every other
+// thread's reads of y behind them, and y is read past the L1 (peers wrote it over NVLink into this GPU's memory).
 __global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __restrict__ y, float* __restrict__ v,
                                                                int N, int32_t* __restrict__ converged_flag,
-                                                               int32_t* __restrict__ iters_done) {
+                                                               int32_t* __restrict__ iters_done,
+                                                               const int32_t* __restrict__ wait_flags, int world, int seq) {
     if (*converged_flag) return;
+    if (wait_flags) {
+        if ((int)threadIdx.x < world) {
+            long long spins = 0;
+            while (ld_acquire_sys(wait_flags + threadIdx.x) < seq) {
+                __nanosleep(64);
+                if (++spins > (1ll << 24)) __trap();          // ~2 s
+            }
+        }
+        __syncthreads();
+    }
     __shared__ double red[32];
     __shared__ int red_close[32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double ss = 0.0;
-    for (int i = threadIdx.x; i < N; i += blockDim.x) ss += (double)y[i] * (double)y[i];
+    for (int i = threadIdx.x; i < N; i += blockDim.x) { const float yi = __ldcg(y + i); ss += (double)yi * (double)yi; }
     ss = warp_sum(ss);
     if (lane == 0) red[warp] = ss;
     __syncthreads();
@@ -119,7 +177,7 @@ __global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __re
     const float nrm = (float)sqrt(tot);
     int close = 1;
     for (int i = threadIdx.x; i < N; i += blockDim.x) {
-        const float vn = __fdiv_rn(y[i], nrm + 1e-6f);
+        const float vn = __fdiv_rn(__ldcg(y + i), nrm + 1e-6f);
         const float vl = v[i];
         close &= (fabsf(vn - vl) <= 1e-8f + 1e-5f * fabsf(vl)) ? 1 : 0;
         v[i] = vn;
@@ -145,10 +203,45 @@ int launch_compat_matvec(const float* src, const float* tgt, const float* v, flo
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st) {
     const int rows = row_end - row_begin;
     if (rows <= 0) return PDSC_OK;
-    compat_matvec_kernel<<<dim3((rows + MV_ROWS - 1) / MV_ROWS, MV_KS), MV_THREADS, 0, st>>>(
-        src, tgt, v, y, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag);
+    compat_matvec_kernel<false><<<dim3((rows + MV_ROWS - 1) / MV_ROWS, MV_KS), MV_THREADS, 0, st>>>(
+        src, tgt, v, y, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, MvPeers{});
     count_launches(1);
     return check_launch("compat_matvec");
+}
+
+// Exchange buffer of the P2P run, one per rank, in memory every peer can address (symmetric memory):
+//   [y parity 0: N floats | y parity 1: N floats | flags: PDSC_P2P_MAX_WORLD int32 | done counter: int32], 256-byte aligned parts
+static size_t p2p_y_bytes(int N) { return align_up(sizeof(float) * (size_t)N, 256); }
+size_t power_p2p_exchange_bytes(int N) { return 2 * p2p_y_bytes(N) + 256; }
+
+int launch_compat_matvec_p2p(const float* src, const float* tgt, const float* v, int N, int row_begin, int row_end,
+                             float sigma_spat, const int32_t* converged_flag, void* const* peer_bases, int world, int rank,
+                             int seq, cudaStream_t st) {
+    const int rows = row_end - row_begin;
+    MvPeers peers;
+    for (int p = 0; p < world; ++p) {
+        char* base = reinterpret_cast<char*>(peer_bases[p]);
+        peers.y[p] = reinterpret_cast<float*>(base + (size_t)(seq & 1) * p2p_y_bytes(N));
+        peers.flags[p] = reinterpret_cast<int32_t*>(base + 2 * p2p_y_bytes(N));
+    }
+    peers.done = peers.flags[rank] + PDSC_P2P_MAX_WORLD;
+    peers.world = world; peers.rank = rank; peers.seq = seq;
+    // (a rank with no rows still has to publish its arrival: one cluster with an empty row range does it)
+    const int nblk = rows > 0 ? (rows + MV_ROWS - 1) / MV_ROWS : 1;
+    compat_matvec_kernel<true><<<dim3(nblk, MV_KS), MV_THREADS, 0, st>>>(
+        src, tgt, v, nullptr, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, peers);
+    count_launches(1);
+    return check_launch("compat_matvec_p2p");
+}
+
+int launch_power_normalize_p2p(void* exchange_base, float* v, int N, int32_t* converged_flag, int32_t* iters_done, int world,
+                               int seq, cudaStream_t st) {
+    char* base = reinterpret_cast<char*>(exchange_base);
+    const float* y = reinterpret_cast<const float*>(base + (size_t)(seq & 1) * p2p_y_bytes(N));
+    const int32_t* flags = reinterpret_cast<const int32_t*>(base + 2 * p2p_y_bytes(N));
+    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done, flags, world, seq);
+    count_launches(1);
+    return check_launch("power_normalize_p2p");
 }
 
 size_t power_workspace(int N) { return align_up(sizeof(float) * (size_t)N, 256) + 256; }
@@ -156,7 +249,7 @@ size_t power_workspace(int N) { return align_up(sizeof(float) * (size_t)N, 256) 
 int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,
                            size_t ws_bytes, cudaStream_t st) {
     (void)ws; (void)ws_bytes;
-    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done);
+    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done, nullptr, 0, 0);
     count_launches(1);
     return check_launch("power_normalize");
 }

@@ -130,7 +130,9 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
             constexpr uint32_t idesc = umma_idesc_f16(128, 128);
             uint32_t acc = 0;
 #pragma unroll
-            for (int term = 0; term < 3; ++term) {
+            // cross terms first (hi*lo, lo*hi, then hi*hi): see mlp.cu
+            for (int ti = 0; ti < 3; ++ti) {
+                const int term = ti == 2 ? 0 : ti + 1;
                 const uint32_t a_lo = term == 2 ? (2u * QK_BLK) >> 4 : 0u, b_lo = term == 1 ? (2u * QK_BLK) >> 4 : 0u;
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {
