@@ -218,6 +218,19 @@ int pdsc_compat_matvec_p2p(const float* src, const float* tgt, const float* v, i
 int pdsc_power_normalize_p2p(void* exchange_base, float* v_inout, int N, int32_t* converged_flag,
                              int32_t* iters_done, int world, int seq, void* stream);
 
+/* No counterpart in the reference.  pdsc_power_iter_full for callers that
+ *  cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): same kernels
+ *  and same results, but the scratch (y[N], the converged flag, the iteration counter) is a file-scope device array
+ *  inside the library instead of a caller-supplied workspace.  The entry point calls no cudaMalloc / cudaFree and no
+ *  allocating library routine; the caller still owns src, tgt, v_out [N] and iters_out [1] (may be NULL).
+ *  Limit: N <= PDSC_POWER_ITER_STATIC_MAX_N (larger N returns PDSC_ERR_ARG; use pdsc_power_iter_full).  Every GPU that
+ *  loads the library holds the array (256 KB + 256 B) until exit.  All calls on a device share it and it keeps the last
+ *  call's contents (each call resets what it needs): calls that overlap on the GPU (different streams) race; calls
+ *  enqueued on one stream are safe. */
+#define PDSC_POWER_ITER_STATIC_MAX_N 65536
+int pdsc_power_iter_full_static(const float* src, const float* tgt, float* v_out, int N,
+                                float sigma_spat, int num_iterations, int32_t* iters_out, void* stream);
+
 /* ---- next rows: the callers either side of the forward -------------------------------------------- */
 
 /* (N2) nearest neighbour in descriptor space; replaces find_nn algorithms/matching.py:22-65 and the

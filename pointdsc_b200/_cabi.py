@@ -71,6 +71,7 @@ SIGNATURES = {
     "pdsc_compat_matvec_p2p": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_void_p]),
     "pdsc_power_normalize_p2p": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pdsc_power_iter_full_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p, c_void_p]),
     "pdsc_power_iter_full": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p,
                                      c_void_p, c_size_t, c_void_p]),
 }
@@ -423,6 +424,7 @@ def power_iter_full(src, tgt, sigma_spat, num_iterations, ws=None):
     return v, iters
 
 
+POWER_ITER_STATIC_MAX_N = 65536
 P2P_MAX_WORLD = 8
 
 
@@ -449,6 +451,20 @@ def power_normalize_p2p(exchange_ptr, v, converged_flag, iters_done, world, seq)
     _check(rc, "pdsc_power_normalize_p2p")
     _count()
     return v
+
+
+def power_iter_full_static(src, tgt, sigma_spat, num_iterations, v_out, iters_out=None):
+    """pdsc_power_iter_full_static: as power_iter_full, but the library's own static device scratch is used and NOTHING
+    is allocated here either -- the caller passes the outputs (v_out [N] fp32, iters_out [1] int32 or None).
+    N <= POWER_ITER_STATIC_MAX_N; calls that overlap on the GPU share the scratch and race."""
+    lib = load()
+    N = src.shape[0]
+    rc = lib.pdsc_power_iter_full_static(_ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"),
+                                         _ptr(v_out, torch.float32, "v_out"), N, float(sigma_spat), int(num_iterations),
+                                         _ptr(iters_out, torch.int32, "iters_out"), _stream())
+    _check(rc, "pdsc_power_iter_full_static")
+    _count()
+    return v_out
 
 
 MATCH_DOT, MATCH_L2 = 0, 1

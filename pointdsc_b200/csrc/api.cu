@@ -288,6 +288,13 @@ int pdsc_power_normalize_p2p(void* exchange_base, float* v_inout, int N, int32_t
                                       reinterpret_cast<cudaStream_t>(stream));
 }
 
+int pdsc_power_iter_full_static(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
+                                int32_t* iters_out, void* stream) {
+    PDSC_REQUIRE(src && tgt && v_out, "power_iter_full_static: null pointer");
+    PDSC_REQUIRE(N > 0 && num_iterations > 0, "power_iter_full_static: bad arguments");
+    return power_iter_full_static(src, tgt, v_out, N, sigma_spat, num_iterations, iters_out, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_hybrid_search(const double* pts, int n, double radius, int max_nn, int32_t* idx_out, double* dist2_out,
                        int32_t* count_out, double* normals_out, void* ws, size_t ws_bytes, void* stream) {
     PDSC_REQUIRE(pts && ws && (idx_out || normals_out), "hybrid_search: null pointer");

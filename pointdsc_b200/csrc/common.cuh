@@ -266,6 +266,8 @@ int launch_compat_matvec_p2p(const float* src, const float* tgt, const float* v,
                              int seq, cudaStream_t st);
 int launch_power_normalize_p2p(void* exchange_base, float* v, int N, int32_t* converged_flag, int32_t* iters_done, int world,
                                int seq, cudaStream_t st);
+int power_iter_full_static(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
+                           int32_t* iters_out, cudaStream_t st);
 int power_iter_full(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
                     int32_t* iters_out, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,

@@ -272,4 +272,45 @@ int power_iter_full(const float* src, const float* tgt, float* v_out, int N, flo
     return check_launch("power_iter_full");
 }
 
+// ------------------------------------------------------------------------------------------------
+// No-allocation variant (pdsc_power_iter_full_static): the scratch of power_iter_full (y[N] + the converged flag + the
+// iteration counter) lives in a file-scope device array instead of a caller-supplied workspace, for callers that cannot
+// allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library
+// holds the array (256 KB + 256 B) until exit.  ALL calls on a device share it: calls that overlap on the GPU (different
+// streams) race; calls on one stream are ordered and safe.  Nothing in it has to survive a call: fill_ones_kernel resets
+// the flag and the counter at the start of every call and y is fully written before it is read.
+static __device__ __align__(256) unsigned char g_power_scratch[sizeof(float) * PDSC_POWER_ITER_STATIC_MAX_N + 256];
+
+// In host code `g_power_scratch` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, asked once per device with that device current (cached per host thread and device).
+static int power_static_scratch(void** out) {
+    static thread_local void* cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); set_error("power_iter_full_static: no current CUDA device"); return PDSC_ERR_DEVICE; }
+    if (dev >= 0 && dev < 64 && cached[dev]) { *out = cached[dev]; return PDSC_OK; }
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_power_scratch);
+    if (e != cudaSuccess || !p) {
+        cudaGetLastError();
+        set_error("power_iter_full_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        return PDSC_ERR_CUDA;
+    }
+    if (dev >= 0 && dev < 64) cached[dev] = p;
+    *out = p;
+    return PDSC_OK;
+}
+
+int power_iter_full_static(const float* src, const float* tgt, float* v_out, int N, float sigma_spat, int num_iterations,
+                           int32_t* iters_out, cudaStream_t st) {
+    if (N > PDSC_POWER_ITER_STATIC_MAX_N) {
+        set_error("power_iter_full_static: N=%d exceeds the static scratch (PDSC_POWER_ITER_STATIC_MAX_N=%d); use "
+                  "pdsc_power_iter_full with a caller-supplied workspace", N, PDSC_POWER_ITER_STATIC_MAX_N);
+        return PDSC_ERR_ARG;
+    }
+    void* scratch = nullptr;
+    const int rc = power_static_scratch(&scratch);
+    if (rc != PDSC_OK) return rc;
+    return power_iter_full(src, tgt, v_out, N, sigma_spat, num_iterations, iters_out, scratch, sizeof(g_power_scratch), st);
+}
+
 }  // namespace pdsc
