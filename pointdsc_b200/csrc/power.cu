@@ -13,7 +13,10 @@ namespace cg = cooperative_groups;
 
 namespace pdsc {
 
-constexpr int MV_LANES = 64, MV_RPT = 2, MV_ROWS = MV_LANES * MV_RPT, MV_SLICES = 4, MV_THREADS = MV_LANES * MV_SLICES,
+// 64 rows per cluster (32 lanes x 2 rows per thread), 8 column slices per CTA (one warp each: every lane of a warp reads the
+// same column, a shared-memory broadcast).  Round 1 used 128 rows x 4 slices: a rank that owns N/8 = 6250 rows then launched
+// 392 CTAs, a third of one wave on 148 SMs; with 64-row blocks it launches 784 and the single-GPU run 6256.
+constexpr int MV_LANES = 32, MV_RPT = 2, MV_ROWS = MV_LANES * MV_RPT, MV_SLICES = 8, MV_THREADS = MV_LANES * MV_SLICES,
               MV_TILE = 512;
 constexpr int MV_KS = 8;        // column splits = CTAs per cluster
 
@@ -23,7 +26,7 @@ __device__ __forceinline__ float mv_fma_sat(float a, float b, float c) {
     return d;
 }
 
-// y[r] = sum_j M[r,j] v[j], M[r,j] = max(0, 1 - (|s_r - s_j| - |t_r - t_j|)^2 / sigma^2), M[r,r] = 0, for 128 rows per
+// y[r] = sum_j M[r,j] v[j], M[r,j] = max(0, 1 - (|s_r - s_j| - |t_r - t_j|)^2 / sigma^2), M[r,r] = 0, for MV_ROWS (64) rows per
 // CLUSTER of 8 CTAs: CTA k of the cluster takes the k-th eighth of the column tiles, the eight partial sums meet in
 // distributed shared memory and rank 0 adds them in a fixed order.  The split does not depend on the row range, so a
 // row-sharded run (any number of ranks) produces the same bits as a single GPU, and a rank that owns only N/8 rows still
@@ -31,7 +34,7 @@ __device__ __forceinline__ float mv_fma_sat(float a, float b, float c) {
 // owns two rows as the two lanes of packed f32x2 adds / FMAs, distances by sqrt.approx (MUFU), 1 - c^2 by one saturating
 // FMA: 2 MUFU + ~9 packed FP32 instructions per pair of entries (the exact-rounding form it replaces cost ~50 per entry).
 //
-// P2P = true (row-sharded run over NVLink, config 4): rank 0 of every cluster stores its 128 results straight into the y
+// P2P = true (row-sharded run over NVLink, config 4): rank 0 of every cluster stores its 64 results straight into the y
 // buffer of EVERY rank (peer device pointers into symmetric memory; y is indexed by the global row, so there is no
 // padding and no gather step), and the last cluster of the grid to finish (device-scope counter) publishes this rank's
 // arrival: a system-scope release store of `seq` into flag slot `rank` of every peer.  The normalise kernel of each rank
@@ -86,7 +89,7 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
             tb[t] = make_float4(tgt[j * 3] * inv_sigma, tgt[j * 3 + 1] * inv_sigma, tgt[j * 3 + 2] * inv_sigma, 0.f);
         }
         __syncthreads();
-        // slice s takes elements s, s+4, ... of the tile: a fixed order, so y is reproducible
+        // slice s takes elements s, s + MV_SLICES, ... of the tile: a fixed order, so y is reproducible
         const int d0 = r0 - j0, d1 = r1 - j0;                 // tile positions of the two diagonal entries (if inside)
 #pragma unroll 4
         for (int t = slice; t < nj; t += MV_SLICES) {
@@ -111,8 +114,11 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
     part[slice][rl] = acc;
     __syncthreads();
     if (slice == 0) {
+        static_assert(MV_SLICES == 8, "fixed-order tree below");
         const float2 p0 = part[0][rl], p1 = part[1][rl], p2 = part[2][rl], p3 = part[3][rl];
-        csum[rl] = make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+        const float2 p4 = part[4][rl], p5 = part[5][rl], p6 = part[6][rl], p7 = part[7][rl];
+        csum[rl] = make_float2(((p0.x + p1.x) + (p2.x + p3.x)) + ((p4.x + p5.x) + (p6.x + p7.x)),
+                               ((p0.y + p1.y) + (p2.y + p3.y)) + ((p4.y + p5.y) + (p6.y + p7.y)));
     }
     cluster.sync();
     if (ks == 0 && slice == 0) {
@@ -146,14 +152,24 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
     cluster.sync();                                           // peers keep their shared memory until rank 0 has read it
 }
 
+// v_new = y / (|y| + 1e-6), the allclose test against v_last, the iteration counter: ONE cluster of PN_CTAS CTAs (the kernel
+// every rank repeats on the whole y each iteration, so its latency is not divided by the number of GPUs: one CTA took ~45 us
+// for N=50000, two passes of 49 dependent loads per thread).  Every CTA sums the squares of its slice in double, the
+// partial sums meet in distributed shared memory and every CTA adds all of them in the same fixed order, so all CTAs (and
+// all ranks) hold the same norm; the "all close" votes are combined the same way.
 // wait_flags != nullptr (P2P run): y is complete once every rank's arrival flag has reached `seq`; the waiting threads poll
 // with system-scope acquire loads (bounded: a lost peer traps instead of hanging the GPU), the barrier orders every other
 // thread's reads of y behind them, and y is read past the L1 (peers wrote it over NVLink into this GPU's memory).
-__global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __restrict__ y, float* __restrict__ v,
-                                                               int N, int32_t* __restrict__ converged_flag,
-                                                               int32_t* __restrict__ iters_done,
-                                                               const int32_t* __restrict__ wait_flags, int world, int seq) {
-    if (*converged_flag) return;
+constexpr int PN_CTAS = 8, PN_THREADS = 1024;
+__global__ void __cluster_dims__(PN_CTAS, 1, 1) __launch_bounds__(PN_THREADS)
+power_normalize_kernel(const float* __restrict__ y, float* __restrict__ v, int N, int32_t* __restrict__ converged_flag,
+                       int32_t* __restrict__ iters_done, const int32_t* __restrict__ wait_flags, int world, int seq) {
+    if (*converged_flag) return;                             // uniform over the cluster (nobody has written it yet: see the end)
+    cg::cluster_group cluster = cg::this_cluster();
+    __shared__ double red[32];
+    __shared__ int red_close[32];
+    __shared__ double cta_sum;                               // read by the peers through DSMEM
+    __shared__ int cta_close;
     if (wait_flags) {
         if ((int)threadIdx.x < world) {
             long long spins = 0;
@@ -164,19 +180,25 @@ __global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __re
         }
         __syncthreads();
     }
-    __shared__ double red[32];
-    __shared__ int red_close[32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rank = (int)cluster.block_rank();
+    const int per = (N + PN_CTAS - 1) / PN_CTAS, i0 = rank * per, i1 = min(N, i0 + per);
     double ss = 0.0;
-    for (int i = threadIdx.x; i < N; i += blockDim.x) { const float yi = __ldcg(y + i); ss += (double)yi * (double)yi; }
+    for (int i = i0 + (int)threadIdx.x; i < i1; i += PN_THREADS) { const float yi = __ldcg(y + i); ss += (double)yi * (double)yi; }
     ss = warp_sum(ss);
     if (lane == 0) red[warp] = ss;
     __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int w = 0; w < 32; ++w) tot += red[w];
+        cta_sum = tot;
+    }
+    cluster.sync();
     double tot = 0.0;
-    for (int w = 0; w < 32; ++w) tot += red[w];
+    for (int c = 0; c < PN_CTAS; ++c) tot += *cluster.map_shared_rank(&cta_sum, c);
     const float nrm = (float)sqrt(tot);
     int close = 1;
-    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    for (int i = i0 + (int)threadIdx.x; i < i1; i += PN_THREADS) {
         const float vn = __fdiv_rn(__ldcg(y + i), nrm + 1e-6f);
         const float vl = v[i];
         close &= (fabsf(vn - vl) <= 1e-8f + 1e-5f * fabsf(vl)) ? 1 : 0;
@@ -188,9 +210,16 @@ __global__ void __launch_bounds__(1024) power_normalize_kernel(const float* __re
     if (threadIdx.x == 0) {
         int all = 1;
         for (int w = 0; w < 32; ++w) all &= red_close[w];
-        if (all) *converged_flag = 1;
+        cta_close = all;
+    }
+    cluster.sync();
+    if (rank == 0 && threadIdx.x == 0) {
+        int all = 1;
+        for (int c = 0; c < PN_CTAS; ++c) all &= *cluster.map_shared_rank(&cta_close, c);
+        if (all) *converged_flag = 1;                        // (every CTA read the flag before the first cluster.sync)
         if (iters_done) *iters_done += 1;
     }
+    cluster.sync();                                          // peers keep their shared memory until rank 0 has read it
 }
 
 __global__ void fill_ones_kernel(float* v, int N, int32_t* flag, int32_t* iters) {
@@ -239,7 +268,7 @@ int launch_power_normalize_p2p(void* exchange_base, float* v, int N, int32_t* co
     char* base = reinterpret_cast<char*>(exchange_base);
     const float* y = reinterpret_cast<const float*>(base + (size_t)(seq & 1) * p2p_y_bytes(N));
     const int32_t* flags = reinterpret_cast<const int32_t*>(base + 2 * p2p_y_bytes(N));
-    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done, flags, world, seq);
+    power_normalize_kernel<<<PN_CTAS, PN_THREADS, 0, st>>>(y, v, N, converged_flag, iters_done, flags, world, seq);
     count_launches(1);
     return check_launch("power_normalize_p2p");
 }
@@ -249,7 +278,7 @@ size_t power_workspace(int N) { return align_up(sizeof(float) * (size_t)N, 256) 
 int launch_power_normalize(const float* y, float* v, int N, int32_t* converged_flag, int32_t* iters_done, void* ws,
                            size_t ws_bytes, cudaStream_t st) {
     (void)ws; (void)ws_bytes;
-    power_normalize_kernel<<<1, 1024, 0, st>>>(y, v, N, converged_flag, iters_done, nullptr, 0, 0);
+    power_normalize_kernel<<<PN_CTAS, PN_THREADS, 0, st>>>(y, v, N, converged_flag, iters_done, nullptr, 0, 0);
     count_launches(1);
     return check_launch("power_normalize");
 }
