@@ -341,6 +341,7 @@ struct PpParams {
     int NU;                 // work units per pair: 256-row blocks (no cluster) or 512-row block pairs (cluster of 2)
     long long total_steps;  // B * NU * NT
     int qk_terms, pv_terms, dbg;   // hi/lo product terms issued per contraction
+    uint32_t hint_soft, hint_role; // suspend-time hints (ns) of the barrier waits of the softmax warps / the role warps
     long long* trace;       // optional timeline of CTA 0 (PDSC_ATTN_TRACE): trace[step * 16 + event] = SM clock
 };
 
@@ -472,20 +473,21 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const uint64_t q_desc0 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[0])));
         const uint64_t q_desc1 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[1])));
         const int qk_terms = p.qk_terms, pv_terms = p.pv_terms;
+        const uint32_t hr = p.hint_role;
         long long pos = lo;
         PpSeg s;
         uint32_t kt = 0;
         for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
             const int n = s.j1 - s.j0;
             // S_A(0), S_B(0)
-            mbar_wait_uniform(&sm.k_full[kt & 1], (kt >> 1) & 1);
+            mbar_wait_uniform(&sm.k_full[kt & 1], (kt >> 1) & 1, hr);
             {
                 const uint64_t kd = pp_uniform64(k_desc[kt & 1]);
-                mbar_wait_uniform(&sm.q_full[0], si & 1);
+                mbar_wait_uniform(&sm.q_full[0], si & 1, hr);
                 tc_fence_after();
                 pp_issue_qk<0>(q_desc0, kd, qk_terms);
                 umma_commit_elect(&sm.s_full[0]);
-                mbar_wait_uniform(&sm.q_full[1], si & 1);
+                mbar_wait_uniform(&sm.q_full[1], si & 1, hr);
                 tc_fence_after();
                 pp_issue_qk<1>(q_desc1, kd, qk_terms);
                 umma_commit_elect(&sm.s_full[1]);
@@ -499,15 +501,15 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 if (CHAIN && t == next_chain) next_chain += p.chain;
                 const uint32_t acc = (t == 0 || (CHAIN && t + p.chain == next_chain)) ? 0u : 1u;     // a fresh chain overwrites O
                 // ---- sub-tile A ----
-                mbar_wait_uniform(&sm.p_full[0], kt & 1);
+                mbar_wait_uniform(&sm.p_full[0], kt & 1, hr);
                 PP_TRACE(kt, 2);
-                mbar_wait_uniform(&sm.v_full[st], (kt >> 1) & 1);
+                mbar_wait_uniform(&sm.v_full[st], (kt >> 1) & 1, hr);
                 PP_TRACE(kt, 12);
                 tc_fence_after();
                 pp_issue_pv<0>(vd, pv_terms, acc);
                 umma_commit_elect(&sm.pv_done[0]);
                 if (more) {
-                    mbar_wait_uniform(&sm.k_full[nx], ((kt + 1) >> 1) & 1);
+                    mbar_wait_uniform(&sm.k_full[nx], ((kt + 1) >> 1) & 1, hr);
                     tc_fence_after();
                     PP_TRACE(kt, 13);
                     pp_issue_qk<0>(q_desc0, kd, qk_terms);
@@ -515,7 +517,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 }
                 PP_TRACE(kt, 4);
                 // ---- sub-tile B ----
-                mbar_wait_uniform(&sm.p_full[1], kt & 1);
+                mbar_wait_uniform(&sm.p_full[1], kt & 1, hr);
                 PP_TRACE(kt, 3);
                 tc_fence_after();
                 pp_issue_pv<1>(vd, pv_terms, acc);
@@ -546,6 +548,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const int dbg = DBG ? p.dbg : 0;
         constexpr bool pv3 = PV3;
         const int N = p.N;
+        const uint32_t hs = p.hint_soft;
         long long pos = lo;
         PpSeg s;
         uint32_t kt = 0;
@@ -587,7 +590,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 const int j = s.j0 + t;
                 // compatibilities of this thread's row against its 32 keys (needs only the points)
                 float2 e[NP];
-                mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1);
+                mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1, hs);
                 // (the never-taken constant branch also fences the compat block: without it ptxas spreads the
                 // compat arithmetic over the following waits and the kernel runs ~6% slower)
                 if (DBG ? (dbg & 1) : (N < 0)) {
@@ -599,7 +602,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm.pts_empty[st]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 6 + x);
-                mbar_wait_role(&sm.s_full[x], kt & 1);
+                mbar_wait_role(&sm.s_full[x], kt & 1, hs);
                 if ((warp & 7) == 0) PP_TRACE(kt, 8 + x);
                 tc_fence_after();
                 // e = compat * S - m  (log2 units), and its maximum over this row's keys
@@ -640,7 +643,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = __fadd2_rn(e[i], ns);
                     if (t > t_chain) {                 // (the first PV of a chain overwrites O: nothing to rescale yet)
-                        mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);      // PV(t-1) has finished accumulating into O
+                        mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);      // PV(t-1) has finished accumulating into O
                         tc_fence_after();
 #pragma unroll
                         for (int c = 0; c < 2; ++c) {
@@ -694,7 +697,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 if (CHAIN && t < n) {
                     // Chain limit: the finished chain's O and its reference max go to this thread's slot of the workspace (stores
                     // only: nothing waits for them); the first PV of the next chain overwrites O (accumulate = 0).
-                    mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);          // PV(t-1) has finished accumulating into O
+                    mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);          // PV(t-1) has finished accumulating into O
                     tc_fence_after();
                     const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + (t / p.chain - 1)) * 2 + x) * PP_SUB + row;
                     float* ca = p.chain_o + slot * PP_C + half * 64;
@@ -713,7 +716,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             } while (CHAIN && t < n);
             // ---- epilogue of the segment ----
             l += __shfl_xor_sync(0xffffffffu, l, 16);
-            mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1);
+            mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);
             tc_fence_after();
             // O of the segment = the last chain (TMEM) + the finished chains (workspace slots, each relative to the reference
             // max it was stored with)
@@ -955,6 +958,9 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
     }
     // PDSC_ATTN_DBG (tuning build): selects the debug instantiation; bits 1 / 2 / 4 switch off the compat arithmetic,
     // the exp, the MMAs (timing experiments only, results are then wrong); 8 sets no knob
+    // PDSC_ATTN_HINT_SOFT / _ROLE (tuning build): suspend-time hints of the mbarrier waits, ns
+    p.hint_soft = (uint32_t)tuning_int("PDSC_ATTN_HINT_SOFT", 20000);
+    p.hint_role = (uint32_t)tuning_int("PDSC_ATTN_HINT_ROLE", 20000);
     const int dbg = tuning_int("PDSC_ATTN_DBG", 0);
     p.dbg = dbg;
     if (dbg & 4) p.qk_terms = p.pv_terms = 0;       // no MMAs

@@ -54,15 +54,15 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
         : "memory");
     return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait_role(uint64_t* bar, uint32_t parity) {
-    for (uint32_t spin = 0; !mbar_try_wait_hint(bar, parity, 20000u); ++spin) {
-        if (spin > (1u << 22)) __trap();
+__device__ __forceinline__ void mbar_wait_role(uint64_t* bar, uint32_t parity, uint32_t hint_ns = 20000u) {
+    for (uint32_t spin = 0; !mbar_try_wait_hint(bar, parity, hint_ns); ++spin) {
+        if (spin > (1u << 26)) __trap();
     }
 }
 // Whole spin loop inside one asm statement: the compiler sees no data-dependent branch, so a warp that
 // waits with all its lanes stays provably convergent (values derived from uniform inputs can then live
 // in uniform registers, which is what tcgen05.mma operands want).
-__device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity, uint32_t hint_ns = 20000u) {
     asm volatile(
         "{\n\t.reg .pred p, q;\n\t.reg .u32 spin;\n\t"
         "mov.u32 spin, 0;\n\t"
@@ -70,11 +70,11 @@ __device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra WAIT_DONE_%=;\n\t"
         "add.u32 spin, spin, 1;\n\t"
-        "setp.gt.u32 q, spin, 4194304;\n\t"      // a mis-programmed pipeline traps instead of hanging the GPU
+        "setp.gt.u32 q, spin, 67108864;\n\t"     // a mis-programmed pipeline traps instead of hanging the GPU
         "@q trap;\n\t"
         "bra WAIT_LOOP_%=;\n\t"
         "WAIT_DONE_%=:\n\t}"
-        ::"r"(smem_u32(bar)), "r"(parity), "r"(20000u)
+        ::"r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
         : "memory");
 }
 
