@@ -23,13 +23,8 @@
 //                warp ever waits for another warp inside a tile.
 //   warp 16      producer: bulk-async (TMA engine) copies of K, V^T, key-point and Q_lo tiles
 //   warp 17      MMA issuer (one elected lane), owns the TMEM allocation
-// TMEM columns: three S/P buffers [0,64) [64,128) [128,192) that ROTATE between the two sub-tiles, O_A [192,320),
-// O_B [320,448), Qhi_A [448,512) (Q_hi of sub-tile B is read from shared memory).  P overwrites S in place as fp16 pairs
-// (hi: columns 0..31, lo: 32..63 of the buffer).  Work item g = 2 * tile + sub-tile uses buffer g % 3, so Q K^T of item
-// g + 3 is issued right behind P V of item g -- i.e. the S of a sub-tile's NEXT key tile is being computed while its
-// softmax warps are still busy with the current one.  (Round 1 had one S buffer per sub-tile: softmax(j) -> P V(j) +
-// Q K^T(j+1) -> softmax(j+1) was one serial chain, and the wait for S was 26 % of all warp samples,
-// profiles/r02_ncu_attn_pp_before.txt.)
+// TMEM columns: S_A [0,64) S_B [64,128) O_A [128,256) O_B [256,384) Qhi_A [384,448) Qhi_B [448,512).
+// P overwrites S in place as fp16 pairs (hi: columns 0..31, lo: 32..63 of the S block).
 #include "common.cuh"
 #include "sm100.cuh"
 
@@ -61,32 +56,21 @@ constexpr uint32_t PP_PTS_BYTES = PP_PTS_FLOATS * 4;
 // row maximum stay normal numbers and down to 2^-30 subnormal (they were flushed 2^6 earlier with the maximum at 2^0).
 constexpr float PP_RESCALE_LOG2 = 14.0f;
 constexpr float PP_TOP_LOG2 = 6.0f;
-constexpr uint32_t PT_S = 0, PT_O = 192, PT_Q = 448;
-constexpr int PP_SBUF = 3;                   // rotating S/P buffers
+constexpr uint32_t PT_S = 0, PT_O = 128, PT_Q = 384;
 constexpr int PP_SOFT_WARPS = 16;
 constexpr int PP_DEFAULT_CLUSTER = 1;                  // CTAs per cluster unless PDSC_ATTN_CLUSTER says otherwise
 constexpr int PP_THREADS = (PP_SOFT_WARPS + 4) * 32;   // + one warpgroup of role warps (producer, MMA issuer, 2 idle)
 
 struct PpSmem {
     uint8_t qlo[2][PP_QLO_BYTES];
-    uint8_t qhi_b[PP_QLO_BYTES];              // Q_hi of sub-tile B (A operand of its hi terms; sub-tile A's sits in TMEM)
     uint8_t k[2][PP_KTILE_BYTES];
     uint8_t v[2][PP_VTILE_BYTES];
+    float4 pts[2][PP_PTS_FLOATS / 4 + 3];     // (+3: stages stay 64-byte aligned)
     uint64_t q_full[2], q_free;
-    uint64_t k_full[2], k_empty[2], v_full[2], v_empty[2];
-    // pv_done[x][tile & 1]: the softmax warps wait on it only now and then (O rescale, chain flush, epilogue) and, with
-    // Q K^T running ahead, may get there while P V of the tile BEFORE the one they ask about is still in flight; a single
-    // parity barrier would then be two phases behind and the wait would fall through.  Alternating between two barriers
-    // keeps the waiter at most one phase ahead of each.
-    uint64_t s_full[PP_SBUF], p_full[PP_SBUF], pv_done[2][2];
-    uint64_t war_bar;                         // debug instantiation only (PDSC_ATTN_DBG bit 16)
+    uint64_t k_full[2], k_empty[2], v_full[2], v_empty[2], pts_full[2], pts_empty[2];
+    uint64_t s_full[2], p_full[2], pv_done[2];
     uint32_t tmem_base;
-    int last_flag[2];
 };
-// 227 KB is all there is (224 KB of operand tiles: Q_lo x2, Q_hi of sub-tile B, two stages of K and V^T).  The key points of a
-// tile (1.5 KB, read identically by all 16 softmax warps) therefore do not get shared-memory stages: they are read from
-// global memory through the L1 (ld.global.nc), the next tile's lines prefetched one tile ahead.
-static_assert(sizeof(PpSmem) + 1024 <= 232448, "PpSmem exceeds the 227 KB of dynamic shared memory per CTA");
 
 // byte offset of (row r, 16-byte chunk c) inside a block of 128-byte rows with the 128B swizzle
 __host__ __device__ inline uint32_t pp_swz(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
@@ -246,61 +230,56 @@ __device__ __forceinline__ uint64_t pp_uniform64(uint64_t v) {
     "setp.eq.b32 pt, 0, 0;\n\t"                                                      \
     "mov.b32 td, %2;\n\tmov.b32 idc, %3;\n\tmov.b64 db, %0;\n\t"
 
-// 8 k-steps, A from TMEM columns a0 + 8 kk, B = 64-row blocks of 8 KB (k-steps 0..3 in block 0, 4..7 in block 1).
-// d / a0: TMEM column addresses (warp-uniform run-time values: the S/P buffer rotates).
-__device__ __forceinline__ void pp_qk_run_ts(uint32_t d, uint32_t a0, uint64_t k_desc, uint32_t acc_first) {
+// 8 k-steps, A from TMEM columns A0 + 8 kk, B = 64-row blocks of 8 KB (k-steps 0..3 in block 0, 4..7 in block 1)
+template <uint32_t D, uint32_t A0>
+__device__ __forceinline__ void pp_qk_run_ts(uint64_t k_desc, uint32_t acc_first) {
     asm volatile(PP_HEAD "mov.b32 ta, %4;\n\t"
                  "@pe tcgen05.mma.cta_group::1.kind::f16 [td], [ta], db, idc, p0;\n\t"
                  PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS
                  PP_ADV_TS(506) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS "}"
-                 ::"l"(k_desc), "r"(acc_first), "r"(d), "n"(umma_idesc_f16(128, 64)), "r"(a0)
+                 ::"l"(k_desc), "r"(acc_first), "n"(D), "n"(umma_idesc_f16(128, 64)), "n"(A0)
                  : "memory");
 }
-// same with A from shared memory (Q_lo, or Q_hi of sub-tile B: 128-row blocks of 16 KB)
-__device__ __forceinline__ void pp_qk_run_ss(uint32_t d, uint64_t q_desc, uint64_t k_desc, uint32_t acc_first) {
+// same with A from shared memory (Q_lo: 128-row blocks of 16 KB)
+template <uint32_t D>
+__device__ __forceinline__ void pp_qk_run_ss(uint64_t q_desc, uint64_t k_desc, uint32_t acc_first) {
     asm volatile(PP_HEAD "mov.b64 da, %4;\n\t"
                  "@pe tcgen05.mma.cta_group::1.kind::f16 [td], da, db, idc, p0;\n\t"
                  PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS
                  PP_ADV_SS(1018, 506) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS PP_ADV_SS(2, 2) PP_SS "}"
-                 ::"l"(k_desc), "r"(acc_first), "r"(d), "n"(umma_idesc_f16(128, 64)), "l"(q_desc)
+                 ::"l"(k_desc), "r"(acc_first), "n"(D), "n"(umma_idesc_f16(128, 64)), "l"(q_desc)
                  : "memory");
 }
-// 4 k-steps, A = P from TMEM columns a0 + 8 kk, B = one 128-row block (V^T half)
-__device__ __forceinline__ void pp_pv_run(uint32_t d, uint32_t a0, uint64_t v_desc, uint32_t acc_first) {
+// 4 k-steps, A = P from TMEM columns A0 + 8 kk, B = one 128-row block (V^T half)
+template <uint32_t D, uint32_t A0>
+__device__ __forceinline__ void pp_pv_run(uint64_t v_desc, uint32_t acc_first) {
     asm volatile(PP_HEAD "mov.b32 ta, %4;\n\t"
                  "@pe tcgen05.mma.cta_group::1.kind::f16 [td], [ta], db, idc, p0;\n\t"
                  PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS PP_ADV_TS(2) PP_TS "}"
-                 ::"l"(v_desc), "r"(acc_first), "r"(d), "n"(umma_idesc_f16(128, 128)), "r"(a0)
+                 ::"l"(v_desc), "r"(acc_first), "n"(D), "n"(umma_idesc_f16(128, 128)), "n"(A0)
                  : "memory");
 }
 
-// S[128 x 64 keys] = Q K^T into the S/P buffer at TMEM column `sp`.  terms: bit 0 = Qhi Khi, bit 1 = Qhi Klo, bit 2 = Qlo Khi
-// (0 = no MMAs: timing experiments).  Sub-tile A reads Q_hi from TMEM, sub-tile B from shared memory (qhi_desc).
+// S_X[128 x 64 keys] = Q K^T.  terms: bit 0 = Qhi Khi, bit 1 = Qhi Klo, bit 2 = Qlo Khi (0 = no MMAs: timing experiments).
 constexpr int PP_QK_HH = 1, PP_QK_HL = 2, PP_QK_LH = 4;
 // The fp32 accumulator in TMEM is updated with truncation (measured in round 1), once per MMA, at the magnitude of the
 // running sum.  The two cross terms are ~2^-11 of the main term, so they go FIRST: their 16 accumulations then truncate at
 // 2^-11 of the logit's magnitude and only the 8 hi*hi accumulations at the full one (24 before: about a third of the bias).
 template <int X>
-__device__ __forceinline__ void pp_issue_qk(uint32_t sp, uint64_t qlo_desc, uint64_t qhi_desc, uint64_t k_desc, int terms) {
+__device__ __forceinline__ void pp_issue_qk(uint64_t qlo_desc, uint64_t k_desc, int terms) {
     if (!(terms & PP_QK_HH)) return;
     uint32_t acc = 0u;
-    if (terms & PP_QK_LH) { pp_qk_run_ss(sp, qlo_desc, k_desc, acc); acc = 1u; }
-    if (X == 0) {
-        if (terms & PP_QK_HL) { pp_qk_run_ts(sp, PT_Q, pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), acc); acc = 1u; }
-        pp_qk_run_ts(sp, PT_Q, k_desc, acc);
-    } else {
-        if (terms & PP_QK_HL) { pp_qk_run_ss(sp, qhi_desc, pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), acc); acc = 1u; }
-        pp_qk_run_ss(sp, qhi_desc, k_desc, acc);
-    }
+    if (terms & PP_QK_LH) { pp_qk_run_ss<PT_S + 64u * X>(qlo_desc, k_desc, acc); acc = 1u; }
+    if (terms & PP_QK_HL) { pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(pp_desc_add(k_desc, 2u * PP_KBLK_BYTES), acc); acc = 1u; }
+    pp_qk_run_ts<PT_S + 64u * X, PT_Q + 64u * X>(k_desc, acc);
 }
-// O_X[128 x 128 ch] (+)= P[128 x 64 keys] V, P in the S/P buffer at column `sp`.
-// terms = 3: Phi Vhi + Phi Vlo + Plo Vhi; 2: Phi Vhi + Phi Vlo; 1: Phi Vhi.
+// O_X[128 x 128 ch] (+)= P[128 x 64 keys] V.  terms = 3: Phi Vhi + Phi Vlo + Plo Vhi; 2: Phi Vhi + Phi Vlo; 1: Phi Vhi.
 template <int X>
-__device__ __forceinline__ void pp_issue_pv(uint32_t sp, uint64_t v_desc, int terms, uint32_t acc) {
+__device__ __forceinline__ void pp_issue_pv(uint64_t v_desc, int terms, uint32_t acc) {
     if (terms <= 0) return;
-    pp_pv_run(PT_O + 128u * X, sp, v_desc, acc);
-    if (terms > 1) pp_pv_run(PT_O + 128u * X, sp, pp_desc_add(v_desc, PP_VHALF_BYTES), 1u);
-    if (terms > 2) pp_pv_run(PT_O + 128u * X, sp + 32u, v_desc, 1u);
+    pp_pv_run<PT_O + 128u * X, PT_S + 64u * X>(v_desc, acc);
+    if (terms > 1) pp_pv_run<PT_O + 128u * X, PT_S + 64u * X>(pp_desc_add(v_desc, PP_VHALF_BYTES), 1u);
+    if (terms > 2) pp_pv_run<PT_O + 128u * X, PT_S + 64u * X + 32u>(v_desc, 1u);
 }
 
 __device__ __forceinline__ float pp_fma_sat(float a, float b, float c) {
@@ -317,7 +296,7 @@ template <int NP>
 __device__ __forceinline__ void pp_compat_pairs(const float4* pts, const float2 (&qp)[6], float2 (&w)[NP]) {
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
-        const float4 pa = __ldg(pts + 3 * i), pb = __ldg(pts + 3 * i + 1), pc = __ldg(pts + 3 * i + 2);
+        const float4 pa = pts[3 * i], pb = pts[3 * i + 1], pc = pts[3 * i + 2];
         float2 dx = __fadd2_rn(qp[0], make_float2(-pa.x, -pa.y));
         float2 dy = __fadd2_rn(qp[1], make_float2(-pa.z, -pa.w));
         float2 dz = __fadd2_rn(qp[2], make_float2(-pb.x, -pb.y));
@@ -408,7 +387,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // the 128B swizzle is anchored at 1024-byte boundaries of the shared window
     PpSmem& sm = *reinterpret_cast<PpSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
-    int* last_flag = sm.last_flag;
+    __shared__ int last_flag[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x / CL, cta = blockIdx.x;        // G work ranges; range index = cluster index
     const int rank = CL == 1 ? 0 : (int)cluster_ctarank();
@@ -420,15 +399,13 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
+            mbar_init(&sm.q_full[i], PP_SOFT_WARPS / 2 + 1);
             mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], CL);     // released by the MMA issuer of every CTA in the cluster
             mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], CL);
-            mbar_init(&sm.pv_done[i][0], 1); mbar_init(&sm.pv_done[i][1], 1);
+            mbar_init(&sm.pts_full[i], 1); mbar_init(&sm.pts_empty[i], PP_SOFT_WARPS);
+            mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], PP_SOFT_WARPS / 2); mbar_init(&sm.pv_done[i], 1);
         }
-        mbar_init(&sm.q_full[0], PP_SOFT_WARPS / 2 + 1);     // sub-tile A: its 8 softmax warps (Q_hi -> TMEM) + the Q_lo copy
-        mbar_init(&sm.q_full[1], 1);                         // sub-tile B: Q_lo and Q_hi both arrive by bulk copy
-        for (int i = 0; i < PP_SBUF; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], PP_SOFT_WARPS / 2); }
         mbar_init(&sm.q_free, 1);
-        mbar_init(&sm.war_bar, 1);
         fence_barrier_init();
     }
     if (warp == PP_SOFT_WARPS + 1) tmem_alloc(&sm.tmem_base, 512);
@@ -457,10 +434,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 const size_t kt0 = (size_t)b * (4 * p.NRBp);               // first 64-key tile of the pair
                 if (si > 0) mbar_wait_role(&sm.q_free, (si - 1) & 1);      // all MMAs of the previous segment are done
                 for (int x = 0; x < 2; ++x) {
-                    mbar_arrive_expect_tx(&sm.q_full[x], x == 0 ? PP_QLO_BYTES : 2 * PP_QLO_BYTES);
+                    mbar_arrive_expect_tx(&sm.q_full[x], PP_QLO_BYTES);
                     bulk_g2s(sm.qlo[x], p.Qw + (q128 + x) * PP_QTILE_BYTES + PP_QLO_OFF, PP_QLO_BYTES, &sm.q_full[x]);
                 }
-                bulk_g2s(sm.qhi_b, p.Qw + (q128 + 1) * PP_QTILE_BYTES, PP_QLO_BYTES, &sm.q_full[1]);   // hi image = first 32 KB of the tile
                 for (int j = s.j0; j < s.j1; ++j, ++kt) {
                     const int st = kt & 1;
                     const uint32_t par = ((kt >> 1) - 1) & 1;               // previous use of this stage
@@ -473,6 +449,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                         bulk_g2s_multicast(sm.k[st] + rank * part, p.Kw + (kt0 + j) * PP_KTILE_BYTES + rank * part, part, &sm.k_full[st], CL_MASK);
                     }
                     PP_TRACE(kt, 0);
+                    if (kt >= 2) mbar_wait_role(&sm.pts_empty[st], par);
+                    mbar_arrive_expect_tx(&sm.pts_full[st], PP_PTS_BYTES);
+                    bulk_g2s(sm.pts[st], p.Pw + (kt0 + j) * PP_PTS_FLOATS, PP_PTS_BYTES, &sm.pts_full[st]);
                     if (kt >= 2) mbar_wait_role(&sm.v_empty[st], par);
                     mbar_arrive_expect_tx(&sm.v_full[st], PP_VTILE_BYTES);
                     if (CL == 1) {
@@ -489,77 +468,69 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         // ============================== MMA issuer ==============================
         // The whole warp runs this loop (warp-uniform control flow keeps the descriptors in uniform
         // registers); only the tcgen05 instructions themselves are predicated on an elected lane.
-        // Work items of a segment: q = 2 t + x (key tile t, sub-tile x); item q uses S/P buffer (g0 + q) % 3, g0 = items of
-        // all earlier segments.  Order on the tensor pipe: QK(0) QK(1) QK(2), then for q = 0, 1, ...: PV(q), QK(q + 3) -- the
-        // pipe executes in issue order, so QK(q + 3) overwrites the buffer only after PV(q) has read P from it.
         const uint64_t k_desc[2] = {umma_desc_sw128_kmajor(smem_u32(sm.k[0])), umma_desc_sw128_kmajor(smem_u32(sm.k[1]))};
         const uint64_t v_desc[2] = {umma_desc_sw128_kmajor(smem_u32(sm.v[0])), umma_desc_sw128_kmajor(smem_u32(sm.v[1]))};
         const uint64_t q_desc0 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[0])));
         const uint64_t q_desc1 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qlo[1])));
-        const uint64_t qh_desc1 = pp_uniform64(umma_desc_sw128_kmajor(smem_u32(sm.qhi_b)));
         const int qk_terms = p.qk_terms, pv_terms = p.pv_terms;
         const uint32_t hr = p.hint_role;
         long long pos = lo;
         PpSeg s;
-        uint32_t kt0 = 0;                        // key tiles of all earlier segments (stage parities, buffer rotation)
-        uint32_t war_phase = 0;
+        uint32_t kt = 0;
         for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
-            const int n = s.j1 - s.j0, m = 2 * n;
-            // Q K^T of item q (waits for its K tile and, on the first tile, for its Q operands)
-            auto issue_qk = [&](int q) {
-                const int t = q >> 1, x = q & 1;
-                const uint32_t kt = kt0 + (uint32_t)t, g = 2u * kt + (uint32_t)x, sb = g % 3u, sp = PT_S + 64u * sb;
+            const int n = s.j1 - s.j0;
+            // S_A(0), S_B(0)
+            mbar_wait_uniform(&sm.k_full[kt & 1], (kt >> 1) & 1, hr);
+            {
                 const uint64_t kd = pp_uniform64(k_desc[kt & 1]);
-                if (x == 0) {
-                    mbar_wait_uniform(&sm.k_full[kt & 1], (kt >> 1) & 1, hr);
-                    if (t == 0) mbar_wait_uniform(&sm.q_full[0], si & 1, hr);
+                mbar_wait_uniform(&sm.q_full[0], si & 1, hr);
+                tc_fence_after();
+                pp_issue_qk<0>(q_desc0, kd, qk_terms);
+                umma_commit_elect(&sm.s_full[0]);
+                mbar_wait_uniform(&sm.q_full[1], si & 1, hr);
+                tc_fence_after();
+                pp_issue_qk<1>(q_desc1, kd, qk_terms);
+                umma_commit_elect(&sm.s_full[1]);
+                if (CL == 1) umma_commit_elect(&sm.k_empty[kt & 1]); else umma_commit_elect_multicast(&sm.k_empty[kt & 1], CL_MASK);
+            }
+            int next_chain = CHAIN ? p.chain : 0;     // first tile of the next accumulation chain
+            for (int t = 0; t < n; ++t, ++kt) {
+                const int st = kt & 1, nx = st ^ 1;
+                const bool more = t + 1 < n;
+                const uint64_t vd = pp_uniform64(v_desc[st]), kd = pp_uniform64(k_desc[nx]);
+                if (CHAIN && t == next_chain) next_chain += p.chain;
+                const uint32_t acc = (t == 0 || (CHAIN && t + p.chain == next_chain)) ? 0u : 1u;     // a fresh chain overwrites O
+                // ---- sub-tile A ----
+                mbar_wait_uniform(&sm.p_full[0], kt & 1, hr);
+                PP_TRACE(kt, 2);
+                mbar_wait_uniform(&sm.v_full[st], (kt >> 1) & 1, hr);
+                PP_TRACE(kt, 12);
+                tc_fence_after();
+                pp_issue_pv<0>(vd, pv_terms, acc);
+                umma_commit_elect(&sm.pv_done[0]);
+                if (more) {
+                    mbar_wait_uniform(&sm.k_full[nx], ((kt + 1) >> 1) & 1, hr);
                     tc_fence_after();
                     PP_TRACE(kt, 13);
-                    pp_issue_qk<0>(sp, q_desc0, 0ull, kd, qk_terms);
-                } else {
-                    if (t == 0) mbar_wait_uniform(&sm.q_full[1], si & 1, hr);
-                    tc_fence_after();
-                    pp_issue_qk<1>(sp, q_desc1, qh_desc1, kd, qk_terms);
+                    pp_issue_qk<0>(q_desc0, kd, qk_terms);
+                    umma_commit_elect(&sm.s_full[0]);
                 }
-                umma_commit_elect(&sm.s_full[sb]);
-                if (x == 1) {                    // both sub-tiles have read this K tile
-                    if (CL == 1) umma_commit_elect(&sm.k_empty[kt & 1]); else umma_commit_elect_multicast(&sm.k_empty[kt & 1], CL_MASK);
-                }
-            };
-            for (int q = 0; q < PP_SBUF && q < m; ++q) issue_qk(q);
-            int next_chain = CHAIN ? p.chain : 0;     // first tile of the next accumulation chain
-            uint32_t acc = 0u;
-            for (int q = 0; q < m; ++q) {
-                const int t = q >> 1, x = q & 1;
-                const uint32_t kt = kt0 + (uint32_t)t, g = 2u * kt + (uint32_t)x, sb = g % 3u, sp = PT_S + 64u * sb;
-                const int st = kt & 1;
-                const uint64_t vd = pp_uniform64(v_desc[st]);
-                if (x == 0) {
-                    if (CHAIN && t == next_chain) next_chain += p.chain;
-                    acc = (t == 0 || (CHAIN && t + p.chain == next_chain)) ? 0u : 1u;     // a fresh chain overwrites O
-                }
-                mbar_wait_uniform(&sm.p_full[sb], (g / 3u) & 1u, hr);
-                PP_TRACE(kt, 2 + x);
-                if (x == 0) {
-                    mbar_wait_uniform(&sm.v_full[st], (kt >> 1) & 1, hr);
-                    PP_TRACE(kt, 12);
-                }
+                PP_TRACE(kt, 4);
+                // ---- sub-tile B ----
+                mbar_wait_uniform(&sm.p_full[1], kt & 1, hr);
+                PP_TRACE(kt, 3);
                 tc_fence_after();
-                if (x == 0) pp_issue_pv<0>(sp, vd, pv_terms, acc); else pp_issue_pv<1>(sp, vd, pv_terms, acc);
-                umma_commit_elect(&sm.pv_done[x][kt & 1]);
-                if (x == 1) {                    // both sub-tiles have read this V tile
-                    if (CL == 1) umma_commit_elect(&sm.v_empty[st]); else umma_commit_elect_multicast(&sm.v_empty[st], CL_MASK);
+                pp_issue_pv<1>(vd, pv_terms, acc);
+                umma_commit_elect(&sm.pv_done[1]);
+                if (CL == 1) umma_commit_elect(&sm.v_empty[st]); else umma_commit_elect_multicast(&sm.v_empty[st], CL_MASK);
+                if (more) {
+                    pp_issue_qk<1>(q_desc1, kd, qk_terms);
+                    umma_commit_elect(&sm.s_full[1]);
+                    if (CL == 1) umma_commit_elect(&sm.k_empty[nx]); else umma_commit_elect_multicast(&sm.k_empty[nx], CL_MASK);
                 }
-                if (DBG && (p.dbg & 16)) {       // experiment: PV(q) has COMPLETED before Q K^T(q + 3) may overwrite its P
-                    umma_commit_elect(&sm.war_bar);
-                    mbar_wait_uniform(&sm.war_bar, war_phase & 1u, hr);
-                    ++war_phase;
-                }
-                if (q + PP_SBUF < m) issue_qk(q + PP_SBUF);
-                PP_TRACE(kt, 4 + x);
+                PP_TRACE(kt, 5);
             }
             umma_commit_elect(&sm.q_free);
-            kt0 += (uint32_t)n;
         }
     } else if (warp < PP_SOFT_WARPS) {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
@@ -570,8 +541,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const int half = lane >> 4;                   // which half of the columns this thread takes
         const int row = quarter * 32 + lh * 16 + (lane & 15);          // query row inside the sub-tile
         const uint32_t lane_addr = (uint32_t)(quarter * 32 + lh * 16) << 16;
+        const uint32_t s_x = tmem + lane_addr + PT_S + 64u * x;
         const uint32_t o_x = tmem + lane_addr + PT_O + 128u * x;
-        const uint32_t q_x = tmem + lane_addr + PT_Q;             // Q_hi of sub-tile A only
+        const uint32_t q_x = tmem + lane_addr + PT_Q + 64u * x;
         const int kp0 = half * NP;                    // first key pair of this thread inside a tile
         const int dbg = DBG ? p.dbg : 0;
         constexpr bool pv3 = PV3;
@@ -586,9 +558,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             const size_t kt0 = (size_t)b * (4 * p.NRBp);
             const int grow = (2 * rb + x) * PP_SUB + row;
             const int qrow = min(grow, N - 1);
-            // ---- Q_hi rows of sub-tile A -> TMEM (this thread: 32 of the 64 words of its row); sub-tile B's Q_hi is read from
-            // shared memory by the MMAs ----
-            if (x == 0) {
+            // ---- Q_hi rows -> TMEM (this thread: 32 of the 64 words of its row) ----
+            {
                 const uint8_t* qsrc = p.Qw + q128 * PP_QTILE_BYTES + (size_t)half * 16384u;   // block `half` = channels 64 half ..
                 uint32_t r[32];
 #pragma unroll
@@ -600,7 +571,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.q_full[0]);
+                if (lane == 0) mbar_arrive(&sm.q_full[x]);
             }
             float2 qp[6];
             {
@@ -617,23 +588,21 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             for (; t < t_end; ++t, ++kt) {
                 const int st = kt & 1;
                 const int j = s.j0 + t;
-                const uint32_t g = 2u * kt + (uint32_t)x, sb = g % 3u;            // work item and its S/P buffer (see the MMA issuer)
-                const uint32_t s_x = tmem + lane_addr + PT_S + 64u * sb;
                 // compatibilities of this thread's row against its 32 keys (needs only the points)
                 float2 e[NP];
-                const float4* ptsg = reinterpret_cast<const float4*>(p.Pw + (kt0 + j) * PP_PTS_FLOATS);
-                if (j + 1 < s.j1 && lane * 128 < (int)PP_PTS_BYTES)       // next tile's key points -> L1
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(ptsg) + PP_PTS_BYTES + lane * 128));
+                mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1, hs);
                 // (the never-taken constant branch also fences the compat block: without it ptxas spreads the
                 // compat arithmetic over the following waits and the kernel runs ~6% slower)
                 if (DBG ? (dbg & 1) : (N < 0)) {
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = make_float2(0.5f, 0.25f);
                 } else {
-                    pp_compat_pairs<NP>(ptsg + kp0 * 3 + half, qp, e);
+                    pp_compat_pairs<NP>(&sm.pts[st][kp0 * 3 + half], qp, e);
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.pts_empty[st]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 6 + x);
-                mbar_wait_role(&sm.s_full[sb], (g / 3u) & 1u, hs);
+                mbar_wait_role(&sm.s_full[x], kt & 1, hs);
                 if ((warp & 7) == 0) PP_TRACE(kt, 8 + x);
                 tc_fence_after();
                 // e = compat * S - m  (log2 units), and its maximum over this row's keys
@@ -674,7 +643,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = __fadd2_rn(e[i], ns);
                     if (t > t_chain) {                 // (the first PV of a chain overwrites O: nothing to rescale yet)
-                        mbar_wait_role(&sm.pv_done[x][(kt - 1) & 1], ((kt - 1) >> 1) & 1, hs);      // PV(t-1) has finished accumulating into O
+                        mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);      // PV(t-1) has finished accumulating into O
                         tc_fence_after();
 #pragma unroll
                         for (int c = 0; c < 2; ++c) {
@@ -722,13 +691,13 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.p_full[sb]);
+                if (lane == 0) mbar_arrive(&sm.p_full[x]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 10 + x);
             }
                 if (CHAIN && t < n) {
                     // Chain limit: the finished chain's O and its reference max go to this thread's slot of the workspace (stores
                     // only: nothing waits for them); the first PV of the next chain overwrites O (accumulate = 0).
-                    mbar_wait_role(&sm.pv_done[x][(kt - 1) & 1], ((kt - 1) >> 1) & 1, hs);          // PV(t-1) has finished accumulating into O
+                    mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);          // PV(t-1) has finished accumulating into O
                     tc_fence_after();
                     const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + (t / p.chain - 1)) * 2 + x) * PP_SUB + row;
                     float* ca = p.chain_o + slot * PP_C + half * 64;
@@ -747,7 +716,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             } while (CHAIN && t < n);
             // ---- epilogue of the segment ----
             l += __shfl_xor_sync(0xffffffffu, l, 16);
-            mbar_wait_role(&sm.pv_done[x][(kt - 1) & 1], ((kt - 1) >> 1) & 1, hs);
+            mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);
             tc_fence_after();
             // O of the segment = the last chain (TMEM) + the finished chains (workspace slots, each relative to the reference
             // max it was stored with)

@@ -1,1 +1,10 @@
-for d in 8 24; do echo "== PDSC_ATTN_DBG=$d"; for n in 256 384 512; do PDSC_ATTN_DBG=$d timeout 100 python scripts/dbg_attn.py $n 0,0,0,3,7 2>&1 | tail -5 | cut -c1-75; done; done
+run() { echo "== $*"; env "$@" python scripts/prof_attn.py split16 16 5000 20 | tail -1 | cut -c1-90; }
+run PDSC_ATTN_DBG=8
+run PDSC_ATTN_DBG=1
+run PDSC_ATTN_DBG=2
+run PDSC_ATTN_DBG=4
+run PDSC_ATTN_DBG=5
+run PDSC_ATTN_QK_TERMS=1
+run PDSC_ATTN_QK_TERMS=3
+run PDSC_ATTN_QK_TERMS=5
+run PDSC_ATTN_PV_TERMS=1

@@ -15,9 +15,12 @@ qkv = torch.randn(B, N, 384, generator=g).cuda()
 src = (torch.rand(B, N, 3, generator=g) * 3).cuda()
 tgt = (torch.rand(B, N, 3, generator=g) * 3).cuda()
 C = 128
-for _ in range(2):
+import time
+t_end = time.perf_counter() + (0.0 if os.environ.get("PROF_NO_WARMUP") else 0.4)      # clocks ramp up from idle over ~100 ms
+n_warm = 0
+while n_warm < 2 or time.perf_counter() < t_end:
     out = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=mode)
-torch.cuda.synchronize()
+    torch.cuda.synchronize(); n_warm += 1
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(reps):
