@@ -2,8 +2,8 @@
 of one box, against the reference CPU path (pattern of the reference's test_parallel.sh:18-24 / test.py:236-257: every
 process takes its share of the pairs, no communication).
 
-One cell per invocation:   python scripts/sweep.py --n 5000                       (1 GPU)
-                           python -m torch.distributed.run --nproc-per-node 4 scripts/sweep.py --n 5000
+One cell per invocation:   python scripts/sweep.py --num-corr 5000                       (1 GPU)
+                           python -m torch.distributed.run --nproc-per-node 4 scripts/sweep.py --num-corr 5000
 Pairs: seeds 1000 .. 5095, 3DMatch parameters, rank r takes the contiguous block parallel.shard_pairs gives it.
 The inputs live in pinned HOST memory; the timed region is the whole job of the rank: per step H2D of one batch, forward,
 D2H of final_trans + final_labels (CUDA events, max over ranks).  Rank 0 also runs the CPU port (oracle/restate.py, all host
@@ -19,7 +19,7 @@ from oracle import restate, synth
 from pointdsc_b200 import PointDSC, _cabi, parallel
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, required=True)
+ap.add_argument("--num-corr", dest="n", type=int, required=True)
 ap.add_argument("--total-pairs", type=int, default=4096)
 ap.add_argument("--batch", type=int, default=0, help="pairs per step per GPU (default: 64 / 16 / 8 at N = 1000 / 5000 / 10000)")
 ap.add_argument("--cpu-pairs", type=int, default=-1)
