@@ -5,6 +5,7 @@
 // correspondence.  Rows are independent, so a rank can own a row range (row sharding) and
 // all-gather y; the normalisation + allclose test is a one-block kernel every rank repeats.
 #include <cooperative_groups.h>
+#include <math.h>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -18,7 +19,7 @@ namespace pdsc {
 // 392 CTAs, a third of one wave on 148 SMs; with 64-row blocks it launches 784 and the single-GPU run 6256.
 constexpr int MV_LANES = 32, MV_RPT = 2, MV_ROWS = MV_LANES * MV_RPT, MV_SLICES = 8, MV_THREADS = MV_LANES * MV_SLICES,
               MV_TILE = 512;
-constexpr int MV_KS = 8;        // column splits = CTAs per cluster
+constexpr int MV_KS = 8;        // most column splits = CTAs per cluster (the launch picks 4..8, see mv_column_splits)
 
 __device__ __forceinline__ float mv_fma_sat(float a, float b, float c) {
     float d;
@@ -56,7 +57,7 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
 }
 
 template <bool P2P>
-__global__ void __cluster_dims__(1, MV_KS, 1) __launch_bounds__(MV_THREADS)
+__global__ void __launch_bounds__(MV_THREADS)
 compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tgt, const float* __restrict__ v,
                      float* __restrict__ y, int N, int row_begin, int row_end, float inv_sigma,
                      const int32_t* __restrict__ converged_flag, const MvPeers peers) {
@@ -77,7 +78,8 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
                  ty = make_float2(tgt[c0 * 3 + 1] * inv_sigma, tgt[c1 * 3 + 1] * inv_sigma),
                  tz = make_float2(tgt[c0 * 3 + 2] * inv_sigma, tgt[c1 * 3 + 2] * inv_sigma);
     const int ntiles = (N + MV_TILE - 1) / MV_TILE;
-    const int t_lo = (int)((long long)ntiles * ks / MV_KS), t_hi = (int)((long long)ntiles * (ks + 1) / MV_KS);
+    const int KS = (int)gridDim.y;                            // column splits = cluster size (launch attribute)
+    const int t_lo = (int)((long long)ntiles * ks / KS), t_hi = (int)((long long)ntiles * (ks + 1) / KS);
     float2 acc = make_float2(0.f, 0.f);
     for (int tile = t_lo; tile < t_hi; ++tile) {
         const int j0 = tile * MV_TILE;
@@ -124,9 +126,10 @@ compat_matvec_kernel(const float* __restrict__ src, const float* __restrict__ tg
     if (ks == 0 && slice == 0) {
         float2 c[MV_KS];
 #pragma unroll
-        for (int k = 0; k < MV_KS; ++k) c[k] = cluster.map_shared_rank(csum, k)[rl];
-        const float y0 = ((c[0].x + c[1].x) + (c[2].x + c[3].x)) + ((c[4].x + c[5].x) + (c[6].x + c[7].x));
-        const float y1 = ((c[0].y + c[1].y) + (c[2].y + c[3].y)) + ((c[4].y + c[5].y) + (c[6].y + c[7].y));
+        for (int k = 0; k < MV_KS; ++k) c[k] = k < KS ? cluster.map_shared_rank(csum, k)[rl] : make_float2(0.f, 0.f);
+        float y0 = c[0].x, y1 = c[0].y;                       // fixed order (the same for every row range and world size)
+#pragma unroll
+        for (int k = 1; k < MV_KS; ++k) if (k < KS) { y0 += c[k].x; y1 += c[k].y; }
         if (!P2P) {
             if (r0 < row_end) y[r0 - row_begin] = y0;
             if (r1 < row_end) y[r1 - row_begin] = y1;
@@ -228,12 +231,44 @@ __global__ void fill_ones_kernel(float* v, int N, int32_t* flag, int32_t* iters)
     if (i == 0) { *flag = 0; *iters = 0; }
 }
 
+// Column splits (= CTAs per cluster) for a pair of N correspondences: a function of N and of the device only -- never of the
+// row range or the world size, so that a row-sharded run adds the same partial sums in the same order as one GPU.  The grid
+// of a rank that owns 1/P of the rows is ceil(N / P / MV_ROWS) clusters; with 4 resident CTAs per SM the last wave is the
+// loss (N = 50000 on 8 GPUs: 98 clusters x 8 = 784 CTAs = 1.32 waves of 592; x 6 = 588, one wave).  The split that loses
+// least over P = 1, 2, 4, 8 wins.
+static int mv_column_splits(int N) {
+    const double resident = 4.0 * num_sms();
+    int best = MV_KS;
+    double best_cost = 1e30;
+    for (int ks = MV_KS; ks >= 4; --ks) {
+        double cost = 0.0;
+        for (int P = 1; P <= 8; P *= 2) {
+            const double ctas = (double)(((N + P - 1) / P + MV_ROWS - 1) / MV_ROWS) * ks;
+            const double waves = ctas / resident;
+            cost += ceil(waves) / waves;
+        }
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = ks; }
+    }
+    return best;
+}
+
+template <bool P2P, typename... Args>
+static void mv_launch(int nblk, int N, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    const int ks = mv_column_splits(N);
+    cfg.gridDim = dim3(nblk, ks); cfg.blockDim = dim3(MV_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = ks; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, compat_matvec_kernel<P2P>, args...);
+}
+
 int launch_compat_matvec(const float* src, const float* tgt, const float* v, float* y, int N, int row_begin,
                          int row_end, float sigma_spat, const int32_t* converged_flag, cudaStream_t st) {
     const int rows = row_end - row_begin;
     if (rows <= 0) return PDSC_OK;
-    compat_matvec_kernel<false><<<dim3((rows + MV_ROWS - 1) / MV_ROWS, MV_KS), MV_THREADS, 0, st>>>(
-        src, tgt, v, y, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, MvPeers{});
+    mv_launch<false>((rows + MV_ROWS - 1) / MV_ROWS, N, st, src, tgt, v, y, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, MvPeers{});
     count_launches(1);
     return check_launch("compat_matvec");
 }
@@ -257,8 +292,7 @@ int launch_compat_matvec_p2p(const float* src, const float* tgt, const float* v,
     peers.world = world; peers.rank = rank; peers.seq = seq;
     // (a rank with no rows still has to publish its arrival: one cluster with an empty row range does it)
     const int nblk = rows > 0 ? (rows + MV_ROWS - 1) / MV_ROWS : 1;
-    compat_matvec_kernel<true><<<dim3(nblk, MV_KS), MV_THREADS, 0, st>>>(
-        src, tgt, v, nullptr, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, peers);
+    mv_launch<true>(nblk, N, st, src, tgt, v, (float*)nullptr, N, row_begin, row_end, 1.0f / sigma_spat, converged_flag, peers);
     count_launches(1);
     return check_launch("compat_matvec_p2p");
 }
