@@ -231,25 +231,19 @@ __global__ void fill_ones_kernel(float* v, int N, int32_t* flag, int32_t* iters)
     if (i == 0) { *flag = 0; *iters = 0; }
 }
 
-// Column splits (= CTAs per cluster) for a pair of N correspondences: a function of N and of the device only -- never of the
-// row range or the world size, so that a row-sharded run adds the same partial sums in the same order as one GPU.  The grid
-// of a rank that owns 1/P of the rows is ceil(N / P / MV_ROWS) clusters; with 4 resident CTAs per SM the last wave is the
-// loss (N = 50000 on 8 GPUs: 98 clusters x 8 = 784 CTAs = 1.32 waves of 592; x 6 = 588, one wave).  The split that loses
-// least over P = 1, 2, 4, 8 wins.
+// Column splits (= CTAs per cluster): 8 for every N and every row range -- never a function of the world size, so that a
+// row-sharded run adds the same partial sums in the same order as one GPU.  Other splits were measured on the row range a
+// rank owns at N = 50000 (scripts/prof_matvec.py, one B200, us per launch):
+//   split   all rows   1/2      1/4      1/8
+//     4      1627      862      447      236
+//     6      1614      833      443      258
+//     8      1624      826      446      235      <- 86 % of 1624 / 8 on 1/8 of the rows
+// (a wave model -- 4 resident CTAs per SM, 6 x 98 clusters = one wave -- predicted 6; the 8-GPU run said 2.95 ms against
+// 2.76 ms with 8.)  PDSC_MV_KS (tuning build) overrides it.
 static int mv_column_splits(int N) {
-    const double resident = 4.0 * num_sms();
-    int best = MV_KS;
-    double best_cost = 1e30;
-    for (int ks = MV_KS; ks >= 4; --ks) {
-        double cost = 0.0;
-        for (int P = 1; P <= 8; P *= 2) {
-            const double ctas = (double)(((N + P - 1) / P + MV_ROWS - 1) / MV_ROWS) * ks;
-            const double waves = ctas / resident;
-            cost += ceil(waves) / waves;
-        }
-        if (cost < best_cost - 1e-9) { best_cost = cost; best = ks; }
-    }
-    return best;
+    (void)N;
+    const int knob = tuning_int("PDSC_MV_KS", 0);
+    return (knob >= 1 && knob <= MV_KS) ? knob : MV_KS;
 }
 
 template <bool P2P, typename... Args>
