@@ -66,6 +66,143 @@ __global__ void __launch_bounds__(NMS_THREADS) nms_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------------------------------
+// pick_seeds, stage 1 on a uniform grid.  The test above is N^2 (190 us for 16 pairs x N=5000, FMA pipe 65 % busy: only
+// fewer tests help).  A point j can only suppress i if |s_i - s_j| < R, so with cubic cells of edge c >= 1.001 R only the
+// 27 cells around i can hold such a j; every candidate found there goes through EXACTLY the arithmetic of nms_kernel
+// (same operations, same rounding, same negated comparisons), so the flags are bit-identical.  Points outside the 27 cells
+// differ from i by more than c in some coordinate; the 0.1 % margin on c covers the fp32 rounding of the cell index and of
+// d2 (both ~1e-7 relative).  Pairs with a non-finite coordinate keep the reference's "NaN suppresses everything below it"
+// behaviour by scanning all j (flag set while the grid is built).
+//   nms_grid_build_kernel  one CTA per pair: bounding box, cell edge c = max(1.001 R, extent / 32 * 1.001) (at most 32^3
+//                          cells: the histogram lives in 128 KB of shared memory), counting sort of the points by cell
+//                          (x fastest) -> records (x, y, z, score) in cell order + cell_start.
+//   nms_grid_test_kernel   one thread per point: 3 x 3 runs of three x-adjacent cells (contiguous in the sorted order).
+// ------------------------------------------------------------------------------------------
+constexpr int NG_MAX = 32, NG_CELLS = NG_MAX * NG_MAX * NG_MAX, NG_THREADS = 1024;
+struct NmsGridHeader { float minx, miny, minz, inv_c; int nx, ny, nz, brute; };
+
+__device__ __forceinline__ int ng_cell(float v, float mn, float inv_c, int n) {
+    const int c = (int)floorf((v - mn) * inv_c);
+    return min(max(c, 0), n - 1);
+}
+
+__global__ void __launch_bounds__(NG_THREADS) nms_grid_build_kernel(const float* __restrict__ src, const float* __restrict__ scores,
+                                                                    int N, float R, NmsGridHeader* __restrict__ hdr,
+                                                                    int* __restrict__ cell_start, float4* __restrict__ rec) {
+    extern __shared__ int hist[];                  // NG_CELLS counters, then (after the scan) running offsets
+    __shared__ float red[6][32];
+    __shared__ int warp_tot[32], bad;
+    __shared__ NmsGridHeader h;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* sb = src + (size_t)b * N * 3;
+    const float* cb = scores + (size_t)b * N;
+    if (tid == 0) bad = 0;
+    float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    bool nonfinite = false;
+    for (int i = tid; i < N; i += NG_THREADS)
+        for (int a = 0; a < 3; ++a) {
+            const float v = sb[i * 3 + a];
+            nonfinite |= !isfinite(v);
+            mn[a] = fminf(mn[a], v); mx[a] = fmaxf(mx[a], v);
+        }
+    for (int a = 0; a < 3; ++a) {
+        float lo = mn[a], hi = mx[a];
+        for (int o = 16; o; o >>= 1) { lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+        if (lane == 0) { red[a][warp] = lo; red[3 + a][warp] = hi; }
+    }
+    __syncthreads();
+    if (nonfinite) bad = 1;
+    for (int c = tid; c < NG_CELLS; c += NG_THREADS) hist[c] = 0;
+    if (tid == 0) {
+        float lo[3], hi[3];
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = red[a][0]; hi[a] = red[3 + a][0];
+            for (int w = 1; w < NG_THREADS / 32; ++w) { lo[a] = fminf(lo[a], red[a][w]); hi[a] = fmaxf(hi[a], red[3 + a][w]); }
+        }
+        const float ext = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), hi[2] - lo[2]);
+        float c = fmaxf(R * 1.001f, ext * (1.001f / NG_MAX));
+        if (!(c > 0.f) || !isfinite(c)) c = 1.0f;
+        h.minx = lo[0]; h.miny = lo[1]; h.minz = lo[2]; h.inv_c = 1.0f / c;
+        h.nx = min(NG_MAX, (int)floorf((hi[0] - lo[0]) / c) + 1);
+        h.ny = min(NG_MAX, (int)floorf((hi[1] - lo[1]) / c) + 1);
+        h.nz = min(NG_MAX, (int)floorf((hi[2] - lo[2]) / c) + 1);
+        h.brute = 0;
+    }
+    __syncthreads();
+    if (tid == 0 && bad) { h.brute = 1; h.nx = h.ny = h.nz = 1; h.minx = h.miny = h.minz = 0.f; h.inv_c = 0.f; }
+    __syncthreads();
+    const NmsGridHeader g = h;
+    const int ncell = g.nx * g.ny * g.nz;
+    for (int i = tid; i < N; i += NG_THREADS) {
+        const int c = (ng_cell(sb[i * 3 + 2], g.minz, g.inv_c, g.nz) * g.ny + ng_cell(sb[i * 3 + 1], g.miny, g.inv_c, g.ny)) * g.nx +
+                      ng_cell(sb[i * 3], g.minx, g.inv_c, g.nx);
+        atomicAdd(&hist[c], 1);
+    }
+    __syncthreads();
+    // exclusive scan of hist[0, ncell): each thread owns a contiguous chunk
+    const int per = (ncell + NG_THREADS - 1) / NG_THREADS, c0 = min(ncell, tid * per), c1 = min(ncell, c0 + per);
+    int sum = 0;
+    for (int c = c0; c < c1; ++c) sum += hist[c];
+    int incl = sum;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int t = warp_tot[lane], inc2 = t;
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, inc2, o); if (lane >= o) inc2 += u; }
+        warp_tot[lane] = inc2 - t;
+    }
+    __syncthreads();
+    int run = warp_tot[warp] + incl - sum;
+    int* cs = cell_start + (size_t)b * (NG_CELLS + 1);
+    for (int c = c0; c < c1; ++c) { const int n = hist[c]; hist[c] = run; cs[c] = run; run += n; }
+    if (tid == 0) { cs[ncell] = N; hdr[b] = g; }
+    __syncthreads();
+    // scatter: the order inside a cell is whatever the atomics give -- the test is an OR over the candidates, so it does not matter
+    float4* rb = rec + (size_t)b * N;
+    for (int i = tid; i < N; i += NG_THREADS) {
+        const float x = sb[i * 3], y = sb[i * 3 + 1], z = sb[i * 3 + 2];
+        const int c = (ng_cell(z, g.minz, g.inv_c, g.nz) * g.ny + ng_cell(y, g.miny, g.inv_c, g.ny)) * g.nx + ng_cell(x, g.minx, g.inv_c, g.nx);
+        rb[atomicAdd(&hist[c], 1)] = make_float4(x, y, z, cb[i]);
+    }
+}
+
+__global__ void __launch_bounds__(256) nms_grid_test_kernel(const float* __restrict__ src, const float* __restrict__ scores, int N,
+                                                            float T2, const NmsGridHeader* __restrict__ hdr,
+                                                            const int* __restrict__ cell_start, const float4* __restrict__ rec,
+                                                            int32_t* __restrict__ suppressed) {
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const NmsGridHeader g = hdr[b];
+    const float xi = src[((size_t)b * N + i) * 3], yi = src[((size_t)b * N + i) * 3 + 1], zi = src[((size_t)b * N + i) * 3 + 2];
+    const float si = scores[(size_t)b * N + i];
+    const float4* rb = rec + (size_t)b * N;
+    const int* cs = cell_start + (size_t)b * (NG_CELLS + 1);
+    bool keep = true;
+    auto test = [&](int j0, int j1) {
+        for (int j = j0; j < j1; ++j) {
+            const float4 q = rb[j];
+            // exactly nms_kernel's arithmetic: d = x_i + (-x_j), squares, (qx + qy) + qz, all rounded to nearest
+            const float dx = __fadd_rn(xi, -q.x), dy = __fadd_rn(yi, -q.y), dz = __fadd_rn(zi, -q.z);
+            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            keep = keep && ((si >= q.w) || (d2 >= T2));
+        }
+    };
+    if (g.brute) {
+        test(0, N);
+    } else {
+        const int cx = ng_cell(xi, g.minx, g.inv_c, g.nx), cy = ng_cell(yi, g.miny, g.inv_c, g.ny), cz = ng_cell(zi, g.minz, g.inv_c, g.nz);
+        const int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.nx - 1);
+        for (int z = max(cz - 1, 0); z <= min(cz + 1, g.nz - 1); ++z)
+            for (int y = max(cy - 1, 0); y <= min(cy + 1, g.ny - 1); ++y) {
+                const int base = (z * g.ny + y) * g.nx;
+                test(cs[base + x0], cs[base + x1 + 1]);
+            }
+    }
+    if (!keep) suppressed[(size_t)b * N + i] = 1;
+}
+
+// ------------------------------------------------------------------------------------------
 // pick_seeds, stage 2: order by (key descending, index ascending), key = score*is_local_max.
 // One CTA per pair, bitonic sort of 64-bit composite keys (all distinct -> deterministic).
 // ------------------------------------------------------------------------------------------
@@ -158,11 +295,15 @@ static int next_pow2(int n) {
 
 constexpr int SORT_SMEM_MAX_ELEMS = 16384;  // 128 KB of 64-bit keys
 
-size_t pick_seeds_workspace(int B, int N) {
-    size_t bytes = align_up(sizeof(int32_t) * (size_t)B * N, 256);
+// workspace: suppressed flags | (large N) global sort buffer | grid: headers, cell_start, point records
+static size_t ps_sort_off(int B, int N) { return align_up(sizeof(int32_t) * (size_t)B * N, 256); }
+static size_t ps_grid_off(int B, int N) {
     const int p2 = next_pow2(N);
-    if (p2 > SORT_SMEM_MAX_ELEMS) bytes += sizeof(unsigned long long) * (size_t)B * p2;
-    return bytes;
+    return ps_sort_off(B, N) + (p2 > SORT_SMEM_MAX_ELEMS ? align_up(sizeof(unsigned long long) * (size_t)B * p2, 256) : 0);
+}
+size_t pick_seeds_workspace(int B, int N) {
+    return ps_grid_off(B, N) + align_up(sizeof(NmsGridHeader) * (size_t)B, 256) + align_up(sizeof(int) * (size_t)B * (NG_CELLS + 1), 256) +
+           sizeof(float4) * (size_t)B * N;
 }
 
 int launch_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds,
@@ -182,13 +323,24 @@ int launch_pick_seeds(const float* src, const float* scores, int B, int N, float
     jsplit = (N + jchunk - 1) / jchunk;
     // squared-distance threshold equivalent to the reference's `norm >= R` (sqrtf is monotone and correctly rounded)
     const float T2 = squared_threshold(R);
-    nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, T2, jchunk, suppressed);
+    // PDSC_NMS_BRUTE=1 (tuning build): the N^2 kernel, which the tests compare the grid kernels with, bit for bit
+    if (tuning_int("PDSC_NMS_BRUTE", 0) != 0 || !(R > 0.f)) {
+        nms_kernel<<<dim3(iblocks, jsplit, B), NMS_THREADS, 0, st>>>(src, scores, N, T2, jchunk, suppressed);
+    } else {
+        char* gbase = reinterpret_cast<char*>(ws) + ps_grid_off(B, N);
+        NmsGridHeader* hdr = reinterpret_cast<NmsGridHeader*>(gbase);
+        int* cell_start = reinterpret_cast<int*>(gbase + align_up(sizeof(NmsGridHeader) * (size_t)B, 256));
+        float4* rec = reinterpret_cast<float4*>(reinterpret_cast<char*>(cell_start) + align_up(sizeof(int) * (size_t)B * (NG_CELLS + 1), 256));
+        opt_in_smem<nms_grid_build_kernel>((int)(sizeof(int) * NG_CELLS));
+        nms_grid_build_kernel<<<B, NG_THREADS, sizeof(int) * NG_CELLS, st>>>(src, scores, N, R, hdr, cell_start, rec);
+        nms_grid_test_kernel<<<dim3((N + 255) / 256, B), 256, 0, st>>>(src, scores, N, T2, hdr, cell_start, rec, suppressed);
+        count_launches(1);
+    }
     const int p2 = next_pow2(N);
     unsigned long long* gbuf = nullptr;
     size_t smem = sizeof(unsigned long long) * (size_t)p2;
     if (p2 > SORT_SMEM_MAX_ELEMS) {
-        gbuf = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) +
-                                                     align_up(sizeof(int32_t) * (size_t)B * N, 256));
+        gbuf = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) + ps_sort_off(B, N));
         smem = 0;
     } else {
         opt_in_smem<seed_order_kernel>((int)(sizeof(unsigned long long) * SORT_SMEM_MAX_ELEMS));

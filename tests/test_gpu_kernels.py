@@ -259,6 +259,49 @@ def test_seed_knn_tensor_core_gram_vs_fp32_gram(N, S, monkeypatch, tuning_lib):
     assert float(differ.float().mean()) < 0.01
 
 
+@pytest.mark.parametrize("shape", ["3dmatch-5000", "kitti-10000", "kitti-50000", "3dmatch-20000", "identical", "line", "duplicates",
+                                   "nan", "tiny-radius", "huge-radius", "n-33"])
+def test_pick_seeds_grid_is_bit_identical_to_brute_force(shape, monkeypatch, tuning_lib):
+    """The uniform-grid local-maximum test (default) against the N^2 kernel (PDSC_NMS_BRUTE=1, tuning build): every flag and
+    every seed equal, on ordinary clouds at all BASELINE sizes (N > 16384 uses the global sort buffer) and on the shapes that
+    stress a grid: one cell, collinear points, exact duplicates, a NaN coordinate, radii far below / above the extent."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(len(shape))
+    R = 0.1
+    if shape.startswith(("3dmatch", "kitti")):
+        fam, N = shape.split("-")
+        cfg = synth.CONFIGS[fam]
+        R = cfg["nms_radius"]
+        src = torch.stack([synth.make_pair(50 + b, int(N), **cfg)["src_keypts"][0] for b in range(2)])
+    elif shape == "identical":
+        src = torch.full((2, 700, 3), 0.25)
+    elif shape == "line":
+        src = torch.zeros(2, 3000, 3); src[:, :, 0] = torch.rand(2, 3000, generator=g) * 5
+    elif shape == "duplicates":
+        base = torch.rand(2, 500, 3, generator=g) * 2
+        src = base.repeat(1, 4, 1)
+    elif shape == "nan":
+        src = torch.rand(2, 900, 3, generator=g) * 3; src[0, 17, 1] = float("nan")
+    elif shape == "tiny-radius":
+        src = torch.rand(2, 4000, 3, generator=g) * 3; R = 1e-4
+    elif shape == "huge-radius":
+        src = torch.rand(2, 1500, 3, generator=g) * 3; R = 100.0
+    else:
+        src = torch.rand(2, 33, 3, generator=g)
+    B, N, _ = src.shape
+    scores = torch.randn(B, N, generator=g)
+    n7 = scores[:, 3::7].shape[1]
+    scores[:, 0:7 * n7:7] = scores[:, 3::7]                                  # equal scores too
+    S = max(1, N // 10)
+    seeds, lm, npos = _cabi.pick_seeds(cu(src), cu(scores), R, S, want_aux=True)
+    monkeypatch.setenv("PDSC_NMS_BRUTE", "1")
+    seeds_b, lm_b, npos_b = _cabi.pick_seeds(cu(src), cu(scores), R, S, want_aux=True)
+    monkeypatch.delenv("PDSC_NMS_BRUTE")
+    assert torch.equal(lm, lm_b), f"{int((lm != lm_b).sum())} local-maximum flags differ"
+    assert torch.equal(seeds, seeds_b) and torch.equal(npos, npos_b)
+    print(f"{shape}: N={N} R={R}: {int(lm.sum())} local maxima, identical to brute force")
+
+
 # ------------------------------------------------------------------------ (d) seed hypotheses
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_hypotheses_vs_reference_golden(case):
