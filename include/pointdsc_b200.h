@@ -200,6 +200,13 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
                          float sigma_spat, int num_iterations, int32_t* iters_out,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* Operand range of the tensor-core paths (pdsc_mlp_chain, pdsc_qkv_pack, pdsc_nonlocal_attn in the SPLIT16 / FP16 modes):
+ *  every fp32 operand is split into fp16 hi + lo, so |value| must stay below 65504 (and relative accuracy degrades below
+ *  ~0.1, absolute error floor ~3e-8).  There is no counterpart in the reference (it computes in fp32).  A kernel that meets
+ *  a value outside the range ORs 1 into *device_flag (int32 in device memory owned by the caller, registered here for the
+ *  calling host thread; NULL unregisters).  The flag is never cleared by the library. */
+int pdsc_set_overflow_flag(int32_t* device_flag);
+
 /* Row-sharded run of the same iteration over NVLink (BASELINE config 4: one pair, N >= 50k, rows split over the GPUs of
  *  one box; cal_leading_eigenvector models/PointDSC.py:338-358).  Instead of an all-gather per iteration, the matvec kernel
  *  of every rank stores its rows straight into the y buffer of EVERY rank (peer pointers into symmetric memory) and then

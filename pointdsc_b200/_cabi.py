@@ -67,6 +67,7 @@ SIGNATURES = {
     "pdsc_nn_match_f64": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "pdsc_icp_refine": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_double, c_int, c_double, c_double, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
+    "pdsc_set_overflow_flag": (c_int, [c_void_p]),
     "pdsc_power_p2p_exchange_bytes": (c_size_t, [c_int]),
     "pdsc_compat_matvec_p2p": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_void_p]),
@@ -422,6 +423,12 @@ def power_iter_full(src, tgt, sigma_spat, num_iterations, ws=None):
     _check(rc, "pdsc_power_iter_full")
     _count()
     return v, iters
+
+
+def set_overflow_flag(flag):
+    """Registers (for this host thread) the int32 device tensor into which the split-fp16 kernels OR 1 when an operand is
+    outside the fp16 range; None unregisters."""
+    _check(load().pdsc_set_overflow_flag(None if flag is None else _ptr(flag, torch.int32, "overflow flag")), "pdsc_set_overflow_flag")
 
 
 POWER_ITER_STATIC_MAX_N = 65536

@@ -53,6 +53,9 @@ const char* tuning_str(const char* name) {
 }
 #endif
 
+static thread_local int32_t* g_overflow_flag = nullptr;
+int32_t* overflow_flag() { return g_overflow_flag; }
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 }  // namespace pdsc
@@ -264,6 +267,11 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
     PDSC_REQUIRE(N > 0 && num_iterations > 0, "power_iter_full: bad arguments");
     return power_iter_full(src, tgt, v_out, N, sigma_spat, num_iterations, iters_out, ws, ws_bytes,
                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+int pdsc_set_overflow_flag(int32_t* device_flag) {
+    g_overflow_flag = device_flag;
+    return PDSC_OK;
 }
 
 size_t pdsc_power_p2p_exchange_bytes(int N) { return N > 0 ? power_p2p_exchange_bytes(N) : 0; }

@@ -40,6 +40,15 @@ static void opt_in_smem(int bytes) {
     if (dev >= 0 && dev < 64) set_bytes[dev] = bytes;
 }
 
+// ---- operand range of the fp16 hi/lo split ------------------------------------------------------
+// A value at or beyond the fp16 range (65504) splits into hi = inf, lo = -inf/NaN; the MMA then produces NaN and the next
+// ReLU turns that NaN into 0: silently wrong numbers.  Every split therefore ORs an "exponent all ones" test of its hi word
+// into a register and, at the end of the kernel, into the caller's flag (pdsc_set_overflow_flag; null = no flag).
+int32_t* overflow_flag();             // the flag registered for the current host thread (device memory owned by the caller)
+__device__ __forceinline__ uint32_t half2_not_finite(uint32_t h2) {     // non-zero if either half is inf or NaN
+    return ((h2 & 0x7c007c00u) + 0x04000400u) & 0x80008000u;
+}
+
 // ---- tuning / debugging knobs ----------------------------------------------------------------
 // The shipped library (libpointdsc_b200.so) is built WITHOUT PDSC_TUNING: every knob is its compile-time default and the
 // environment is never read.  The tests and scripts/ that exercise other launch shapes load libpointdsc_b200_tuning.so,

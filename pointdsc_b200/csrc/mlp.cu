@@ -34,14 +34,16 @@ struct MlpParams {
     uint32_t b_off[ML_MAX_LAYERS];     // float offset of the layer's bias
     uint32_t w_bytes, n_bias;
     int Kp;                            // row length (halves) of the packed output
+    int32_t* overflow;                 // caller's operand-range flag (common.cuh), may be null
 };
 
 __device__ __forceinline__ uint64_t ml_uniform64(uint64_t v) {   // broadcast from lane 0: provably warp-uniform
     const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)v, 0), hi = __shfl_sync(0xffffffffu, (uint32_t)(v >> 32), 0);
     return ((uint64_t)hi << 32) | lo;
 }
-__device__ __forceinline__ void ml_split_pair(float a, float b, uint32_t& hi, uint32_t& lo) {
+__device__ __forceinline__ void ml_split_pair(float a, float b, uint32_t& hi, uint32_t& lo, uint32_t& bad) {
     hi = pack_half2(a, b);
+    bad |= half2_not_finite(hi);
     const float2 back = unpack_half2(hi);
     lo = pack_half2(a - back.x, b - back.y);
 }
@@ -68,6 +70,7 @@ template <int N>
 __device__ __forceinline__ void ml_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParams p) {
+    uint32_t bad = 0;                                       // operand-range test of every split (common.cuh)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     float* bsm = reinterpret_cast<float*>(wsm + p.w_bytes);
@@ -129,8 +132,8 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                 for (int i = 0; i < 8; ++i) {
                     float4 v = xr[c * 8 + i];
                     if (ar) { const float4 a = __ldg(ar + c * 8 + i); v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w; }
-                    ml_split_pair(v.x, v.y, hi[2 * i], lo[2 * i]);
-                    ml_split_pair(v.z, v.w, hi[2 * i + 1], lo[2 * i + 1]);
+                    ml_split_pair(v.x, v.y, hi[2 * i], lo[2 * i], bad);
+                    ml_split_pair(v.z, v.w, hi[2 * i + 1], lo[2 * i + 1], bad);
                 }
                 tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
                 tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
@@ -186,7 +189,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                 if (!last) {
                     uint32_t hi[16], lo[16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+                    for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i], bad);
                     tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
                     tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
                 } else {
@@ -208,7 +211,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
                         uint8_t* pr = p.y_packed + (size_t)row * p.Kp * 2;
                         uint32_t hi[16], lo[16];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+                        for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i], bad);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const uint4 h4 = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
@@ -247,6 +250,7 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
         }
     }
     ml_wait_group<0>();
+    if (bad && p.overflow) atomicOr(p.overflow, 1);
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 256);
@@ -259,6 +263,7 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     MlpParams p;
     p.x = x; p.add_in = add_in; p.add_out = add_out; p.y = y; p.y_packed = reinterpret_cast<uint8_t*>(y_packed);
     p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.rows = rows; p.n_layers = n_layers; p.Kp = Kp;
+    p.overflow = overflow_flag();
     uint32_t woff = 0, boff = 0;
     for (int l = 0; l < n_layers; ++l) {
         const int K = dims[l], N = dims[l + 1];

@@ -37,6 +37,7 @@ struct QkvParams {
     int n_counters;
     int B, N, NT128;
     float qscale, inv_sigma;
+    int32_t* overflow;                 // caller's operand-range flag (common.cuh), may be null
 };
 
 __device__ __forceinline__ uint32_t qk_swz(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
@@ -44,13 +45,15 @@ __device__ __forceinline__ uint64_t qk_uniform64(uint64_t v) {
     const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)v, 0), hi = __shfl_sync(0xffffffffu, (uint32_t)(v >> 32), 0);
     return ((uint64_t)hi << 32) | lo;
 }
-__device__ __forceinline__ void qk_split_pair(float a, float b, uint32_t& hi, uint32_t& lo) {
+__device__ __forceinline__ void qk_split_pair(float a, float b, uint32_t& hi, uint32_t& lo, uint32_t& bad) {
     hi = pack_half2(a, b);
+    bad |= half2_not_finite(hi);
     const float2 back = unpack_half2(hi);
     lo = pack_half2(a - back.x, b - back.y);
 }
 
 __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams p) {
+    uint32_t bad = 0;                                       // operand-range test of every split (common.cuh)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     __shared__ float bsm[128];
@@ -111,8 +114,8 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
             for (int u = 0; u < 16; ++u) {
                 const uint32_t r = (uint32_t)(warp + 8 * u);
                 uint32_t h0, l0, h1, l1;
-                qk_split_pair(v[u].x, v[u].y, h0, l0);
-                qk_split_pair(v[u].z, v[u].w, h1, l1);
+                qk_split_pair(v[u].x, v[u].y, h0, l0, bad);
+                qk_split_pair(v[u].z, v[u].w, h1, l1, bad);
                 const uint32_t off = blk + qk_swz(r, chunk) + sub;
                 *reinterpret_cast<uint2*>(yimg + off) = make_uint2(h0, h1);
                 *reinterpret_cast<uint2*>(yimg + 2 * QK_BLK + off) = make_uint2(l0, l1);
@@ -189,7 +192,7 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
                 for (int j = 0; j < 4; ++j) {
                     uint32_t h[4], l[4];
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) qk_split_pair(v[8 * j + 2 * e], v[8 * j + 2 * e + 1], h[e], l[e]);
+                    for (int e = 0; e < 4; ++e) qk_split_pair(v[8 * j + 2 * e], v[8 * j + 2 * e + 1], h[e], l[e], bad);
                     const uint32_t off = base + ((((uint32_t)(c & 1) * 4u + (uint32_t)j) ^ r7) << 4);
                     *reinterpret_cast<uint4*>(img + off) = make_uint4(h[0], h[1], h[2], h[3]);
                     *reinterpret_cast<uint4*>(img + lo_off + off) = make_uint4(l[0], l[1], l[2], l[3]);
@@ -207,6 +210,7 @@ __global__ void __launch_bounds__(QK_THREADS, 1) qkv_pack_kernel(const QkvParams
         }
     }
     if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (bad && p.overflow) atomicOr(p.overflow, 1);
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x < 32) tmem_dealloc(tmem_base_s, 256);
@@ -223,6 +227,7 @@ int launch_qkv_pack(const float* y, const void* wpack, const float* bias, const 
     p.y = y; p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.src = src; p.tgt = tgt;
     attn_pp_tile_pointers(ws, B, N, &p.Qw, &p.Kw, &p.Vw, &p.Pw, &p.counters, &p.n_counters);
     p.B = B; p.N = N; p.NT128 = attn_pp_tiles128(N);
+    p.overflow = overflow_flag();
     p.qscale = 1.4426950408889634f / sqrtf((float)C);
     p.inv_sigma = 1.0f / sigma_spat;
     const int smem = (int)(3 * QK_IMG + 1024);   // weights + one operand/image buffer per warp group

@@ -30,6 +30,10 @@ from . import _cabi
 _MODE_NAMES = {"fp32": _cabi.ATTN_FP32, "split16": _cabi.ATTN_SPLIT16, "split16pv2": _cabi.ATTN_SPLIT16_PV2,
                "fp16": _cabi.ATTN_FP16}
 _MLP_MODES = ("fused", "split16", "fp32")
+# Supported operand range of the split-fp16 tensor-core paths: fp16 overflows at 65504; below ~6e-5 the lo half goes
+# subnormal, so the absolute error floor of an operand is ~3e-8 (relative accuracy 2^-22 for |x| >= 2^-14 * 2^11 = 0.125,
+# degrading linearly below).  O(1) features and weights -- what BatchNorm produces -- sit in the middle of it.
+FP16_OPERAND_LIMIT = 6.0e4
 
 
 def _pointwise_mlp(dims, norm, last_act):
@@ -129,6 +133,7 @@ class PointDSC(nn.Module):
             raise ValueError(f"POINTDSC_MLP_MODE={self.mlp_mode!r}: expected one of {_MLP_MODES}")
         self._packed = None
         self._ws = _cabi.Workspace()
+        self._overflow = None            # int32 device flag of the split-fp16 kernels (pdsc_set_overflow_flag)
 
     # ---- packed (BN-folded, channel-last) weights; rebuilt whenever parameters may have changed
     def _apply(self, fn, *a, **kw):
@@ -181,6 +186,15 @@ class PointDSC(nn.Module):
         P["cls"] = [(W.contiguous(), b.contiguous()) for W, b in P["cls"]]
         P["cls_w3"] = P["cls"][2][0].reshape(-1).contiguous()
         # one host sync at pack time instead of one per forward
+        # The tensor-core paths split every operand into fp16 hi + lo: a weight (after BatchNorm folding) at or beyond the fp16
+        # range would become inf silently.  Weights are static, so this is checked once here; activations are covered by
+        # the `finite` flag of the result (see _forward_test).  POINTDSC_MLP_MODE=fp32 with POINTDSC_ATTN_MODE=fp32 has no
+        # such limit.
+        if self.mlp_mode != "fp32" or self.attn_mode != _cabi.ATTN_FP32:
+            worst = max(float(t.abs().max()) for L_ in layers for name in ("pcn", "qkv", "m0", "m3", "m6") for t in L_[name])
+            if not worst < FP16_OPERAND_LIMIT:
+                raise ValueError(f"a folded weight or bias has magnitude {worst:.3g}: the fp16 hi/lo operand split supports "
+                                 f"|value| < {FP16_OPERAND_LIMIT:g}; use POINTDSC_MLP_MODE=fp32 and POINTDSC_ATTN_MODE=fp32 for this model")
         P["sigma"] = float(self.sigma.detach().float().item())
         P["sigma_spat"] = float(self.sigma_spat.detach().float().item())
         self._packed = P
@@ -279,6 +293,10 @@ class PointDSC(nn.Module):
     def _forward_test(self, corr_pos, src, tgt):
         P = self._packed or self._pack()
         B, N, _ = corr_pos.shape
+        if self._overflow is None or self._overflow.device != corr_pos.device:
+            self._overflow = torch.zeros(1, dtype=torch.int32, device=corr_pos.device)
+        self._overflow.zero_()
+        _cabi.set_overflow_flag(self._overflow)
         S = int(N * self.ratio)
         if S < 1:
             raise ValueError(f"N={N} gives int(N*ratio)=0 seeds")
@@ -297,6 +315,7 @@ class PointDSC(nn.Module):
                 confidence = self.classify(feat)                             # :171
         finally:
             torch.backends.cuda.matmul.allow_tf32 = prev_tf32
+            _cabi.set_overflow_flag(None)        # (launches already made carry the pointer; nothing else may write to it)
         ws = self._ws
         seeds = _cabi.pick_seeds(src, confidence, self.nms_radius, S, ws=ws)              # :174
         knn_idx = _cabi.seed_knn(normed, seeds, k, ws=ws)                                 # :251-252
@@ -320,4 +339,8 @@ class PointDSC(nn.Module):
             "best_idx": best,
             "initial_trans": initial_trans,
             "corr_features": feat,
+            # device-side flag, no host sync: False when an operand left the range of the fp16 hi/lo split (raised by the
+            # kernels at the split, include/pointdsc_b200.h pdsc_set_overflow_flag) or a confidence is not finite; the
+            # numbers are then NOT to be trusted (an overflow can come back as a finite value after a ReLU)
+            "finite": torch.isfinite(confidence).all() & (self._overflow[0] == 0),
         }

@@ -223,3 +223,75 @@ def test_forward_rejects_inputs_the_reference_cannot_process():
     data["testing"] = True
     with pytest.raises((RuntimeError, ValueError, IndexError)):
         model(data)
+
+
+def test_operand_range_of_the_fp16_split_is_enforced_or_flagged():
+    """the split-fp16 paths have a finite operand range.  A weight beyond it is refused when the weights are
+    packed; activations beyond it surface as res['finite'] == False (never as silently wrong numbers); inside the range
+    -- features and weights scaled by 1e3 and 1e-3 -- the result still matches the oracle."""
+    from pointdsc_b200 import PointDSC
+    cfg = synth.CONFIGS["3dmatch"]
+    L, N = 2, 600
+    pair = synth.make_pair(77, N, **cfg)
+    data = {k: pair[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+
+    def build(mutate):
+        sd = synth.make_state_dict(99, num_layers=L, sigma_d=cfg["sigma_d"])
+        mutate(sd)
+        m = PointDSC(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"]).eval()
+        m.load_state_dict(sd, strict=True)
+        return m.cuda(), sd
+
+    # (a) a folded weight of 1e5: refused
+    def huge_weight(sd):
+        sd["encoder.blocks.PointCN_layer_0.0.weight"][0, 0, 0] = 1.0e5
+    m, _ = build(huge_weight)
+    with pytest.raises(ValueError, match="fp16"):
+        m(data)
+    # (b) activations beyond the range (layer0 scaled by 1e6): flagged, not silent
+    def huge_act(sd):
+        sd["encoder.layer0.weight"] *= 1.0e6
+    m, _ = build(huge_act)
+    assert not bool(m(data)["finite"])
+    # (c) features scaled by 1e3 / 1e-1, with the BatchNorm statistics scaled to match (a tiny or a large running_var, i.e. a
+    # large or a small folded gain), stay accurate
+    for gain in (1.0e3, 1.0e-1):
+        def scaled(sd, gain=gain):
+            sd["encoder.layer0.weight"] *= gain
+            sd["encoder.layer0.bias"] *= gain
+            sd["encoder.blocks.PointCN_layer_0.1.running_var"] *= gain * gain       # BatchNorm undoes the scale again
+            sd["encoder.blocks.PointCN_layer_0.1.running_mean"] *= gain
+        m, sd = build(scaled)
+        res = m(data)
+        assert bool(res["finite"]), (bool(torch.isfinite(res["confidence"]).all()), int(m._overflow[0]))
+        ref = restate.forward_pair(sd, pair["corr_pos"], pair["src_keypts"], pair["tgt_keypts"], num_layers=L,
+                                   inlier_threshold=cfg["inlier_threshold"], nms_radius=cfg["nms_radius"])
+        dconf = float((res["confidence"].cpu() - ref["confidence"]).abs().max())
+        print(f"input gain {gain:g}: max |dconf| {dconf:.2e}")
+        assert dconf <= CONF_TOL * max(1.0, float(ref["confidence"].abs().max()))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process():
+    """the >48 KB dynamic shared memory opt-in is per device; the cache that guards it is keyed by the device, so a
+    process that runs on cuda:0 and then on cuda:1 works on both (it failed with 'invalid argument' on the second device)."""
+    from pointdsc_b200 import PointDSC
+    cfg = synth.CONFIGS["3dmatch"]
+    L, N = 2, 700
+    sd = synth.make_state_dict(99, num_layers=L, sigma_d=cfg["sigma_d"])
+    pair = synth.make_pair(5, N, **cfg)
+    outs = []
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        with torch.cuda.device(dev):
+            m = PointDSC(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"], nms_radius=cfg["nms_radius"]).eval()
+            m.load_state_dict(sd, strict=True)
+            m = m.to(dev)
+            data = {k: pair[k].to(dev) for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+            data["testing"] = True
+            res = m(data)
+            torch.cuda.synchronize(dev)
+            outs.append({k: res[k].cpu() for k in ("final_trans", "confidence", "seeds")})
+    for o in outs[1:]:
+        for k in o:
+            assert torch.equal(o[k], outs[0][k]), k
