@@ -330,9 +330,9 @@ __device__ __forceinline__ void pp_compat_pairs(const float4* pts, const float2 
 struct PpParams {
     const uint8_t* Qw; const uint8_t* Kw; const uint8_t* Vw; const float* Pw;
     float* out; int64_t ld_out;
-    float* part_o;          // [grid][2 slots][2 sub-tiles][128 rows][128 ch]
+    float* part_o;          // [grid][2 slots][2 sub-tiles][64 KB in the owner threads' order, see pp_priv_index]
     float* part_ml;         // [grid][2][2][128][2]  (m, l)
-    float* chain_o;         // [grid][PP_CHAIN_SLOTS][2 sub-tiles][128 rows][128 ch]: O of the finished chains of the current segment
+    float* chain_o;         // [grid][PP_CHAIN_SLOTS][2 sub-tiles][64 KB, pp_priv_index]: O of the finished chains of the current segment
     float* chain_m;         // [grid][PP_CHAIN_SLOTS][2][128]: the reference max each was stored with
     int chain;              // key tiles per accumulation chain (0 = no limit)
     int* counters;          // [B * NRBp][2]
@@ -347,6 +347,7 @@ struct PpParams {
 
 constexpr int PP_CHAIN_SLOTS = 8;     // finished chains per segment that the workspace holds
 struct PpSeg { int blk, j0, j1; };
+// rows 0..239: per key-tile step; rows 240..255: per segment (0/1 segment start A/B, 2/3 body of the segment done, 4/5 last PV seen, 6/7 epilogue done)
 #define PP_TRACE(step, ev) do { if (tracing && (step) < 256) p.trace[(step) * 16 + (ev)] = clock64(); } while (0)
 
 __device__ __forceinline__ long long pp_range_lo(long long total, int c, int G) { return total * c / G; }
@@ -371,6 +372,48 @@ __device__ __forceinline__ float4 pp_ldcg4(const float* p) {
     float4 v;
     asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
+}
+
+// Private order of a sub-tile's O (128 rows x 128 channels) in the workspace (stream-K partials, finished chains): these
+// buffers are written and read back by the thread with the same (warp of the sub-tile, lane), which owns 64 channels of one
+// row as 16 float4 (f = 8 * chunk + i).  Stored as [warp][f][lane] every warp instruction moves 512 contiguous bytes; stored
+// row-major (each lane 128 bytes from its neighbour, as until round 2) it touched 32 lines and the epilogue of a segment
+// spent 14 k clocks in the LSU (profiles/experiments/r02_attn_segment_boundaries.txt).
+__device__ __forceinline__ uint32_t pp_priv_index(int w8, int f, int lane) { return (uint32_t)((w8 * 16 + f) * 32 + lane); }
+
+// In-register transpose of an 8 x 8 matrix of float4 over the 8 lanes of a group (k = lane & 7): before, lane k holds the
+// eight float4 of ITS 128-byte piece; after, it holds float4 number k of the pieces of the lanes 8g .. 8g+7.  A warp store of
+// element j then writes four whole 128-byte lines (one per group) instead of 16 bytes into each of 32 lines.
+__device__ __forceinline__ void pp_transpose8(uint32_t (&r)[32], int k) {
+#pragma unroll
+    for (int m = 1; m < 8; m <<= 1) {
+        const bool up = (k & m) != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (j & m) continue;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t a = r[4 * j + q], b = r[4 * (j | m) + q];
+                const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, m);
+                if (up) r[4 * j + q] = got; else r[4 * (j | m) + q] = got;
+            }
+        }
+    }
+}
+
+// Rows of the output: chunk c (32 channels) of the 64 channels every lane of the warp owns, already scaled.  `tile_row0` =
+// first row of the warp's 16 rows in the pair, lanes 0-15 own channels [0,64) of those rows and lanes 16-31 channels [64,128).
+__device__ __forceinline__ void pp_store_rows(float* out_pair, int64_t ld_out, int tile_row0, int N, int c, uint32_t (&r)[32], int lane) {
+    const int g = lane >> 3, k = lane & 7;
+    pp_transpose8(r, k);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int src_lane = 8 * g + j;
+        const int grow = tile_row0 + (src_lane & 15);
+        if (grow < N)
+            *reinterpret_cast<uint4*>(out_pair + (size_t)grow * ld_out + (src_lane >> 4) * 64 + c * 32 + k * 4) =
+                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -539,6 +582,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const int x = warp >> 3;                      // sub-tile A / B
         const int lh = (warp >> 2) & 1;               // which 16 lanes of the quarter
         const int half = lane >> 4;                   // which half of the columns this thread takes
+        const int w8 = warp & 7;                      // warp inside the sub-tile (order of the private workspace buffers)
         const int row = quarter * 32 + lh * 16 + (lane & 15);          // query row inside the sub-tile
         const uint32_t lane_addr = (uint32_t)(quarter * 32 + lh * 16) << 16;
         const uint32_t s_x = tmem + lane_addr + PT_S + 64u * x;
@@ -550,29 +594,38 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
         const int N = p.N;
         const uint32_t hs = p.hint_soft;
         long long pos = lo;
-        PpSeg s;
+        PpSeg s, s_next;
         uint32_t kt = 0;
-        for (int si = 0; pp_next_segment(pos, hi, NT, s); ++si) {
-            const int b = s.blk / p.NU, rb = (s.blk - b * p.NU) * CL + rank;
+        // Q_hi rows of a segment's block -> TMEM (this thread: 32 of the 64 words of its row), then q_full.  (Handing the next
+        // block's Q_hi over BEFORE the epilogue of its predecessor, with q_free raised after the last Q K^T, was measured: 1-5 %
+        // slower, profiles/experiments/r02_attn_early_q_handover.diff; reading whole rows per 8-lane group + the transpose of
+        // pp_transpose8 instead of a row per lane: no gain, same file.)
+        auto load_q_hi = [&](const PpSeg& sg) {
+            const int b = sg.blk / p.NU, rb = (sg.blk - b * p.NU) * CL + rank;
             const size_t q128 = (size_t)b * (2 * p.NRBp) + 2 * rb + x;
+            const uint8_t* qsrc = p.Qw + q128 * PP_QTILE_BYTES + (size_t)half * 16384u;   // block `half` = channels 64 half ..
+            uint32_t r[32];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint4 v4 = __ldg(reinterpret_cast<const uint4*>(qsrc + pp_swz((uint32_t)row, (uint32_t)i)));
+                r[4 * i] = v4.x; r[4 * i + 1] = v4.y; r[4 * i + 2] = v4.z; r[4 * i + 3] = v4.w;
+            }
+            tmem_st_h32<32>(q_x, r);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.q_full[x]);
+        };
+        bool have = pp_next_segment(pos, hi, NT, s);
+        for (int si = 0; have; ++si) {
+            load_q_hi(s);
+            const int b = s.blk / p.NU, rb = (s.blk - b * p.NU) * CL + rank;
             const size_t kt0 = (size_t)b * (4 * p.NRBp);
             const int grow = (2 * rb + x) * PP_SUB + row;
             const int qrow = min(grow, N - 1);
-            // ---- Q_hi rows -> TMEM (this thread: 32 of the 64 words of its row) ----
-            {
-                const uint8_t* qsrc = p.Qw + q128 * PP_QTILE_BYTES + (size_t)half * 16384u;   // block `half` = channels 64 half ..
-                uint32_t r[32];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const uint4 v4 = __ldg(reinterpret_cast<const uint4*>(qsrc + pp_swz((uint32_t)row, (uint32_t)i)));
-                    r[4 * i] = v4.x; r[4 * i + 1] = v4.y; r[4 * i + 2] = v4.z; r[4 * i + 3] = v4.w;
-                }
-                tmem_st_h32<32>(q_x, r);
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.q_full[x]);
-            }
+            const int warp_row0 = (2 * rb + x) * PP_SUB + quarter * 32 + lh * 16;      // first of this warp's 16 rows in the pair
+            float* out_pair = p.out + (size_t)b * N * p.ld_out;
+            if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 0 + x);
             float2 qp[6];
             {
                 const int qpr = (qrow & 63) >> 1;
@@ -699,37 +752,40 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     // only: nothing waits for them); the first PV of the next chain overwrites O (accumulate = 0).
                     mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);          // PV(t-1) has finished accumulating into O
                     tc_fence_after();
-                    const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + (t / p.chain - 1)) * 2 + x) * PP_SUB + row;
-                    float* ca = p.chain_o + slot * PP_C + half * 64;
+                    const size_t slot = ((size_t)cta * PP_CHAIN_SLOTS + (t / p.chain - 1)) * 2 + x;
+                    uint4* ca = reinterpret_cast<uint4*>(p.chain_o + slot * (PP_SUB * PP_C));
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
                         uint32_t r[32];
                         tmem_ld_h32<64>(o_x + 32u * c, r);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; i += 4)
-                            __stcg(reinterpret_cast<uint4*>(ca + c * 32 + i), make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]));
+                        for (int i = 0; i < 8; ++i)
+                            __stcg(ca + pp_priv_index(w8, c * 8 + i, lane), make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]));
                     }
-                    if (half == 0) __stcg(p.chain_m + slot, m);
+                    if (half == 0) __stcg(p.chain_m + slot * PP_SUB + row, m);
                     t_chain = t;
                 }
             } while (CHAIN && t < n);
             // ---- epilogue of the segment ----
+            const bool have_next = pp_next_segment(pos, hi, NT, s_next);
+            if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 2 + x);
             l += __shfl_xor_sync(0xffffffffu, l, 16);
             mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);
             tc_fence_after();
+            if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 4 + x);
             // O of the segment = the last chain (TMEM) + the finished chains (workspace slots, each relative to the reference
             // max it was stored with)
             const int nflush = CHAIN ? (n - 1) / p.chain : 0;
             auto add_chains = [&](uint32_t (&r)[32], int c) {
                 if (CHAIN) {
                     for (int k = 0; k < nflush; ++k) {
-                        const size_t slot = (((size_t)cta * PP_CHAIN_SLOTS + k) * 2 + x) * PP_SUB + row;
-                        const float4* ca = reinterpret_cast<const float4*>(p.chain_o + slot * PP_C + half * 64 + c * 32);
+                        const size_t slot = ((size_t)cta * PP_CHAIN_SLOTS + k) * 2 + x;
+                        const float4* ca = reinterpret_cast<const float4*>(p.chain_o + slot * (PP_SUB * PP_C));
                         float4 a[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) a[i] = __ldcg(ca + i);          // eight loads in flight
-                        const float f = exp2f(__ldcg(p.chain_m + slot) - m);
+                        for (int i = 0; i < 8; ++i) a[i] = __ldcg(ca + pp_priv_index(w8, c * 8 + i, lane));     // eight loads in flight
+                        const float f = exp2f(__ldcg(p.chain_m + slot * PP_SUB + row) - m);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) + f * a[i].x);
@@ -743,29 +799,21 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             if (s.j0 == 0 && s.j1 == NT) {
                 // all keys seen: msg = O / l, this thread writes 64 channels of its row
                 const float inv_l = 1.0f / l;
-                float* orow = p.out + ((size_t)b * N + qrow) * p.ld_out + half * 64;
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t r[32];
                     tmem_ld_h32<64>(o_x + 32u * c, r);
                     tmem_ld_wait();
                     add_chains(r, c);
-                    if (grow < N) {
 #pragma unroll
-                        for (int i = 0; i < 32; i += 4) {
-                            float4 o;
-                            o.x = __uint_as_float(r[i]) * inv_l;
-                            o.y = __uint_as_float(r[i + 1]) * inv_l;
-                            o.z = __uint_as_float(r[i + 2]) * inv_l;
-                            o.w = __uint_as_float(r[i + 3]) * inv_l;
-                            *reinterpret_cast<float4*>(orow + c * 32 + i) = o;
-                        }
-                    }
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * inv_l);
+                    pp_store_rows(out_pair, p.ld_out, warp_row0, N, c, r, lane);
                 }
             } else {
                 // partial: store (O, m, l); the last contributor of the block combines all partials
-                const size_t base = ((size_t)(cta * 2 + (si == 0 ? 0 : 1)) * 2 + x) * PP_SUB + row;      // cta = rng * CL + rank
-                float* po = p.part_o + base * PP_C + half * 64;
+                const size_t pslot = (size_t)(cta * 2 + (si == 0 ? 0 : 1)) * 2 + x;      // cta = rng * CL + rank
+                const size_t base = pslot * PP_SUB + row;
+                uint4* po = reinterpret_cast<uint4*>(p.part_o + pslot * (PP_SUB * PP_C));
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t r[32];
@@ -773,8 +821,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     tmem_ld_wait();
                     add_chains(r, c);
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4)
-                        *reinterpret_cast<uint4*>(po + c * 32 + i) = make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+                    for (int i = 0; i < 8; ++i)
+                        po[pp_priv_index(w8, c * 8 + i, lane)] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
                 }
                 if (half == 0) {
                     p.part_ml[base * 2] = m;
@@ -791,41 +839,82 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                     // last arrival: leave the counter at zero for the next launch on this workspace
                     if ((warp & 7) == 0 && lane == 0) p.counters[((size_t)b * p.NRBp + rb) * 2 + x] = 0;
                     __threadfence();
+                    // contributor c wrote slot 0 if the block is the first segment of its range, else slot 1: only c_first can
+                    // have started before the block
+                    const int first_slot = pp_range_lo(T, c_first, G) >= x0 ? 0 : 1;
+                    auto part_slot = [&](int c) { return (size_t)((c * CL + rank) * 2 + (c == c_first ? first_slot : 0)) * 2 + x; };
+                    if (c_last == c_first + 1) {
+                        // two contributors (the usual case): every load of a pass is in flight at once; same arithmetic,
+                        // term by term, as the general loop below
+                        const size_t ps0 = part_slot(c_first), ps1 = part_slot(c_last);
+                        const float* ml0 = p.part_ml + (ps0 * PP_SUB + row) * 2;
+                        const float* ml1 = p.part_ml + (ps1 * PP_SUB + row) * 2;
+                        const float m0 = pp_ldcg(ml0), l0 = pp_ldcg(ml0 + 1), m1 = pp_ldcg(ml1), l1 = pp_ldcg(ml1 + 1);
+                        const float M = fmaxf(fmaxf(-INFINITY, m0), m1);
+                        const float f0 = exp2f(m0 - M), f1 = exp2f(m1 - M);
+                        float L = 0.f;
+                        L += f0 * l0;
+                        L += f1 * l1;
+                        const float inv_l = 1.0f / L;
+                        const float* o0 = p.part_o + ps0 * (PP_SUB * PP_C);
+                        const float* o1 = p.part_o + ps1 * (PP_SUB * PP_C);
+#pragma unroll 1
+                        for (int ch = 0; ch < 2; ++ch) {
+                            float4 a0[8], a1[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                a0[i] = pp_ldcg4(o0 + 4 * (size_t)pp_priv_index(w8, ch * 8 + i, lane));
+                                a1[i] = pp_ldcg4(o1 + 4 * (size_t)pp_priv_index(w8, ch * 8 + i, lane));
+                            }
+                            uint32_t r[32];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                float ax = 0.f, ay = 0.f, az = 0.f, aw = 0.f;
+                                ax += f0 * a0[i].x; ay += f0 * a0[i].y; az += f0 * a0[i].z; aw += f0 * a0[i].w;
+                                ax += f1 * a1[i].x; ay += f1 * a1[i].y; az += f1 * a1[i].z; aw += f1 * a1[i].w;
+                                r[4 * i] = __float_as_uint(ax * inv_l); r[4 * i + 1] = __float_as_uint(ay * inv_l);
+                                r[4 * i + 2] = __float_as_uint(az * inv_l); r[4 * i + 3] = __float_as_uint(aw * inv_l);
+                            }
+                            pp_store_rows(out_pair, p.ld_out, warp_row0, N, ch, r, lane);
+                        }
+                    } else {
                     float M = -INFINITY;
-                    for (int c = c_first; c <= c_last; ++c) {
-                        const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
-                        M = fmaxf(M, pp_ldcg(p.part_ml + idx * 2));
-                    }
+                    for (int c = c_first; c <= c_last; ++c) M = fmaxf(M, pp_ldcg(p.part_ml + (part_slot(c) * PP_SUB + row) * 2));
                     float L = 0.f;
                     for (int c = c_first; c <= c_last; ++c) {
-                        const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
-                        L += exp2f(pp_ldcg(p.part_ml + idx * 2) - M) * pp_ldcg(p.part_ml + idx * 2 + 1);
+                        const float* ml = p.part_ml + (part_slot(c) * PP_SUB + row) * 2;
+                        L += exp2f(pp_ldcg(ml) - M) * pp_ldcg(ml + 1);
                     }
                     const float inv_l = 1.0f / L;
-                    float* orow = p.out + ((size_t)b * N + qrow) * p.ld_out + half * 64;
 #pragma unroll 1
-                    for (int ch = 0; ch < 64; ch += 16) {
-                        float acc[16];
+                    for (int ch = 0; ch < 2; ++ch) {                      // 32 channels at a time, as in the direct epilogue
+                        float acc[32];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+                        for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+#pragma unroll 1
                         for (int c = c_first; c <= c_last; ++c) {
-                            const size_t idx = ((size_t)((c * CL + rank) * 2 + (pp_range_lo(T, c, G) >= x0 ? 0 : 1)) * 2 + x) * PP_SUB + row;
-                            const float f = exp2f(pp_ldcg(p.part_ml + idx * 2) - M);
-                            const float* src_o = p.part_o + idx * PP_C + half * 64 + ch;
+                            const size_t ps = part_slot(c);
+                            const float* src_o = p.part_o + ps * (PP_SUB * PP_C);
+                            float4 v4[8];
 #pragma unroll
-                            for (int i = 0; i < 16; i += 4) {
-                                const float4 v4 = pp_ldcg4(src_o + i);
-                                acc[i] += f * v4.x; acc[i + 1] += f * v4.y; acc[i + 2] += f * v4.z; acc[i + 3] += f * v4.w;
+                            for (int i = 0; i < 8; ++i) v4[i] = pp_ldcg4(src_o + 4 * (size_t)pp_priv_index(w8, ch * 8 + i, lane));     // eight loads in flight
+                            const float f = exp2f(pp_ldcg(p.part_ml + (ps * PP_SUB + row) * 2) - M);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                acc[4 * i] += f * v4[i].x; acc[4 * i + 1] += f * v4[i].y; acc[4 * i + 2] += f * v4[i].z; acc[4 * i + 3] += f * v4[i].w;
                             }
                         }
-                        if (grow < N) {
+                        uint32_t r[32];
 #pragma unroll
-                            for (int i = 0; i < 16; i += 4)
-                                *reinterpret_cast<float4*>(orow + ch + i) = make_float4(acc[i] * inv_l, acc[i + 1] * inv_l, acc[i + 2] * inv_l, acc[i + 3] * inv_l);
-                        }
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(acc[i] * inv_l);
+                        pp_store_rows(out_pair, p.ld_out, warp_row0, N, ch, r, lane);
+                    }
                     }
                 }
             }
+            if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 6 + x);
+            s = s_next;
+            have = have_next;
         }
     }
     tc_fence_before();
@@ -1007,9 +1096,15 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
         cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
         if (FILE* f = fopen(trace_path, "w")) {
             fprintf(f, "# step kIssued vIssued pfullA pfullB issuedA issuedB compatA compatB sSeenA sSeenB pArrA pArrB vfull kfullNext (clocks relative to step 0 kIssued)\n");
-            for (int i = 0; i < 256 && h[i * 16]; ++i) {
+            for (int i = 0; i < 240 && h[i * 16]; ++i) {
                 fprintf(f, "%d", i);
                 for (int e = 0; e < 14; ++e) fprintf(f, " %lld", h[i * 16 + e] ? h[i * 16 + e] - h[0] : -1);
+                fprintf(f, "\n");
+            }
+            fprintf(f, "# segment startA startB bodyDoneA bodyDoneB lastPvA lastPvB epiDoneA epiDoneB\n");
+            for (int i = 240; i < 256 && h[i * 16]; ++i) {
+                fprintf(f, "# seg %d", i - 240);
+                for (int e = 0; e < 8; ++e) fprintf(f, " %lld", h[i * 16 + e] ? h[i * 16 + e] - h[0] : -1);
                 fprintf(f, "\n");
             }
             fclose(f);

@@ -1,10 +1,4 @@
-run() { echo "== $*"; env "$@" python scripts/prof_attn.py split16 16 5000 20 | tail -1 | cut -c1-90; }
-run PDSC_ATTN_DBG=8
-run PDSC_ATTN_DBG=1
-run PDSC_ATTN_DBG=2
-run PDSC_ATTN_DBG=4
-run PDSC_ATTN_DBG=5
-run PDSC_ATTN_QK_TERMS=1
-run PDSC_ATTN_QK_TERMS=3
-run PDSC_ATTN_QK_TERMS=5
-run PDSC_ATTN_PV_TERMS=1
+python scripts/ab_attn.py 16 5000 20 head.so final.so qcoal.so
+python scripts/ab_attn.py 64 1000 40 head.so final.so qcoal.so
+python scripts/ab_attn.py 16 10000 8 head.so final.so qcoal.so
+timeout 900 python -m pytest tests/test_gpu_kernels.py -x -q -k "attn or attention" 2>&1 | tail -3

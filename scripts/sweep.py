@@ -146,6 +146,9 @@ if rank == 0:
         mean = sum(times) / len(times)
         line["cpu_baseline"] = {"value": 1.0 / mean, "unit": bench.UNIT, "cores": cores, "kind": "port", "s_per_pair": mean,
                                 "sample": f"{cpu_pairs} pair(s) of this cell after 1 warm-up pair, oracle/restate.py, torch CPU fp32, {cores} threads"}
+        if world > 1:
+            line["cpu_baseline"]["note"] = ("timed while the other ranks' host threads spin in the closing barrier: NOT a baseline; "
+                                            "the CPU figure of a row of the sweep is the 1-GPU cell's")
         line["parity_check"] = {"against": f"oracle/restate.py on the first {cpu_pairs + 1} pairs of the cell", "max_rot_err_deg": worst["rot"],
                                 "max_trans_err_m": worst["trans"], "max_label_mismatches": worst["label_mismatch"],
                                 "ok": worst["rot"] <= 0.01 and worst["trans"] <= 1e-4 and worst["label_mismatch"] <= 2,
