@@ -25,6 +25,9 @@ CASES = {
     "g3_3dmatch_n2000_l12": ("3dmatch", 2000, 12, 3, 99),
     # stress weights (synth.STRESS): sharp attention (|logit| up to ~20 in log2 units), confidences spanning > 1
     "g4_3dmatch_n2000_l12_stress": ("3dmatch", 2000, 12, 5, 99, synth.STRESS),
+    # 40 duplicated / near-duplicated inlier correspondences (synth.make_pair(duplicates=40)): the seed kNN's rank 0 is not
+    # always the seed itself (7th field = extra make_pair arguments)
+    "g5_3dmatch_n1000_l12_dups": ("3dmatch", 1000, 12, 21, 99, {}, dict(duplicates=40)),
 }
 
 
@@ -44,11 +47,16 @@ def weight_kwargs(name):
     return dict(c[5]) if len(c) > 5 else {}
 
 
+def pair_kwargs(name):
+    c = CASES.get(name) or FULL_CASES[name]
+    return dict(c[6]) if len(c) > 6 else {}
+
+
 def case_inputs(name):
     fam, N, L, pair_seed, w_seed = (CASES.get(name) or FULL_CASES[name])[:5]
     cfg = synth.CONFIGS[fam]
     sd = synth.make_state_dict(w_seed, num_layers=L, sigma_d=cfg["sigma_d"], **weight_kwargs(name))
-    pair = synth.make_pair(pair_seed, N, **cfg)
+    pair = synth.make_pair(pair_seed, N, **cfg, **pair_kwargs(name))
     ctor = dict(num_layers=L, inlier_threshold=cfg["inlier_threshold"], sigma_d=cfg["sigma_d"],
                 nms_radius=cfg["nms_radius"])
     return cfg, sd, pair, ctor
@@ -75,7 +83,7 @@ def main(only=None):
         }
         meta = dict(case=name, family=CASES[name][0], N=CASES[name][1], num_layers=CASES[name][2],
                     pair_seed=CASES[name][3], weight_seed=CASES[name][4], ctor=ctor, weight_kwargs=weight_kwargs(name),
-                    torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing)")
+                    pair_kwargs=pair_kwargs(name), torch=torch.__version__, reference="AmnonDrory/PointDSC models/PointDSC.py forward (testing)")
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"),
                             meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8),
                             **{k: v.numpy() for k, v in arrays.items()})

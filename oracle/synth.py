@@ -39,9 +39,12 @@ def random_rotation(gen: torch.Generator) -> torch.Tensor:
 
 
 def make_pair(seed: int, N: int, inlier_ratio: float = 0.10, scale: float = 3.0,
-              noise: float = 0.02, **_unused):
+              noise: float = 0.02, duplicates: int = 0, **_unused):
     """Returns dict(corr_pos [1,N,6], src_keypts [1,N,3], tgt_keypts [1,N,3],
-    gt_trans [4,4], gt_labels [N]) fp32, CPU."""
+    gt_trans [4,4], gt_labels [N]) fp32, CPU.
+    duplicates = d > 0: d outlier correspondences are overwritten with copies of d inlier correspondences -- the first d/2
+    bit for bit, the others moved by 1e-5 of the scale -- so that a seed's nearest neighbour in feature space ties with (or
+    beats) the seed itself (the reference's knn drops rank 0 of topk(k+1), models/common.py:68, assuming it is self)."""
     gen = torch.Generator().manual_seed(int(seed))
     src = torch.rand(N, 3, generator=gen) * scale
     R = random_rotation(gen)
@@ -53,6 +56,12 @@ def make_pair(seed: int, N: int, inlier_ratio: float = 0.10, scale: float = 3.0,
     tgt[inl] = src[inl] @ R.T + t + torch.randn(n_in, 3, generator=gen) * noise
     labels = torch.zeros(N)
     labels[inl] = 1.0
+    if duplicates:
+        d = int(duplicates)
+        assert d <= n_in and n_in + d <= N
+        a, b = inl[:d], perm[n_in:n_in + d]
+        src[b], tgt[b], labels[b] = src[a], tgt[a], 1.0
+        src[b[d // 2:]] += 1e-5 * scale
     corr = torch.cat([src, tgt], dim=-1)
     corr = corr - corr.mean(dim=0, keepdim=True)
     T = torch.eye(4)

@@ -200,6 +200,34 @@ def test_seed_knn_vs_reference_golden(case):
     assert bool((dist[:, :, :-1] <= dist[:, :, 1:]).all())
 
 
+def test_seed_knn_duplicated_correspondences_deviation():
+    """A deliberate, logged deviation: the reference takes topk(k+1) and drops rank 0 assuming it is the
+    seed itself (models/common.py:68); with a duplicated or near-duplicated correspondence rank 0 can be the duplicate, and
+    the reference then KEEPS the seed in its own neighbour list and loses the duplicate -- which of the two depends on its
+    rounding / topk's tie order.  The library always excludes the seed by index.  On the fixture with 40 such duplicates
+    (unmodified reference's output): wherever the two lists differ beyond distance ties, the reference's extra entry is the
+    seed itself and ours is a correspondence with the same coordinates (<= 1e-4), so the point sets the hypothesis is fitted
+    to are the same."""
+    from pointdsc_b200 import _cabi
+    meta, g = load_golden("g5_3dmatch_n1000_l12_dups")
+    normed, seeds, ref = g["normed_features"], g["seeds"], g["knn_idx"]
+    src, tgt = g["src_keypts"][0], g["tgt_keypts"][0]
+    idx = _cabi.seed_knn(cu(normed), cu(seeds), ref.shape[2]).cpu()
+    n_self_rows = 0
+    for s in range(seeds.shape[1]):
+        me = int(seeds[0, s])
+        mine, theirs = set(idx[0, s].tolist()), set(ref[0, s].tolist())
+        assert me not in mine
+        if me in theirs:
+            n_self_rows += 1
+            # the duplicate the reference dropped in favour of the seed is in our list, and it is the same point
+            twins = [j for j in mine - theirs if float((src[j] - src[me]).abs().max()) <= 1e-4 and float((tgt[j] - tgt[me]).abs().max()) <= 1e-4]
+            assert twins, f"seed row {s}: the reference kept the seed itself but no twin of it is in our list"
+    print(f"[deviation] seed_knn: the reference kept the seed in its own neighbour list in {n_self_rows} of {seeds.shape[1]} rows "
+          f"(duplicated correspondences); ours holds the seed's twin there")
+    assert n_self_rows >= 5          # the fixture exercises the case
+
+
 @pytest.mark.parametrize("N,copies", [(300, 4), (5000, 4), (20000, 4), (5000, 500), (20000, 1000)])
 def test_seed_knn_ties_and_long_rows(N, copies):
     """Selection is exact under ties: every feature row appears `copies` times (bit-identical distances), so the

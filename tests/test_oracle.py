@@ -22,7 +22,7 @@ def _run_oracle(meta, g):
 def test_inputs_regenerate(case):
     """The seeded generator reproduces the committed inputs bit for bit."""
     meta, g = load_golden(case)
-    p = synth.make_pair(meta["pair_seed"], meta["N"], **synth.CONFIGS[meta["family"]])
+    p = synth.make_pair(meta["pair_seed"], meta["N"], **synth.CONFIGS[meta["family"]], **meta.get("pair_kwargs", {}))
     for k in ("corr_pos", "src_keypts", "tgt_keypts"):
         assert torch.equal(p[k], g[k]), k
 
