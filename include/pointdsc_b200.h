@@ -204,7 +204,8 @@ int pdsc_power_iter_full(const float* src, const float* tgt, float* v_out, int N
  *  every fp32 operand is split into fp16 hi + lo, so |value| must stay below 65504 (and relative accuracy degrades below
  *  ~0.1, absolute error floor ~3e-8).  There is no counterpart in the reference (it computes in fp32).  A kernel that meets
  *  a value outside the range ORs 1 into *device_flag (int32 in device memory owned by the caller, registered here for the
- *  calling host thread; NULL unregisters).  The flag is never cleared by the library. */
+ *  calling host thread; NULL unregisters).  pdsc_feature_head raises the same flag for a confidence that is not finite.
+ *  The flag is never cleared by the library. */
 int pdsc_set_overflow_flag(int32_t* device_flag);
 
 /* Row-sharded run of the same iteration over NVLink (BASELINE config 4: one pair, N >= 50k, rows split over the GPUs of

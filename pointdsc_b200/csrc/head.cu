@@ -22,6 +22,7 @@ struct HeadParams {
     float* normed; float* conf;
     long long rows;
     float eps;
+    int32_t* overflow;      // caller-owned flag (pdsc_set_overflow_flag) or null: raised when a confidence is not finite
 };
 
 __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadParams p) {
@@ -106,7 +107,9 @@ __global__ void __launch_bounds__(HD_THREADS) feature_head_kernel(const HeadPara
         float c = 0.f;
 #pragma unroll
         for (int o = 0; o < HD_H; ++o) c = fmaf(fmaxf(h2[o] + b2[o], 0.f), w3[o], c);
-        p.conf[row0 + rt] = c + p.b3[0];
+        const float cv = c + p.b3[0];
+        p.conf[row0 + rt] = cv;
+        if (p.overflow && !(fabsf(cv) <= 3.4e38f)) atomicOr(p.overflow, 1);     // inf or NaN (an upstream overflow that survived)
         den[rt] = fmaxf(sqrtf(ss), p.eps);            // F.normalize: x / max(||x||_2, eps)
     }
     __syncthreads();
@@ -131,6 +134,7 @@ int launch_feature_head(const float* feat, long long rows, int C, int H1, int H2
     HeadParams p;
     p.feat = feat; p.w1 = w1t; p.b1 = b1; p.w2 = w2t; p.b2 = b2; p.w3 = w3; p.b3 = b3;
     p.normed = normed; p.conf = conf; p.rows = rows; p.eps = eps;
+    p.overflow = overflow_flag();
     const int smem = (int)sizeof(float) * (128 * HD_PITCH + HD_C * HD_H + HD_H * HD_H + 3 * HD_H + 128 + 128 * (HD_H + 1));
     opt_in_smem<feature_head_kernel>(smem);
     feature_head_kernel<<<(unsigned)((rows + 127) / 128), HD_THREADS, smem, st>>>(p);

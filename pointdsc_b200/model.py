@@ -310,9 +310,11 @@ class PointDSC(nn.Module):
                 # one pass over the features: normalisation (:156) + classifier (:171)
                 normed, confidence = _cabi.feature_head(feat.contiguous(), cls[0][0], cls[0][1], cls[1][0], cls[1][1],
                                                         P["cls_w3"], cls[2][1])
+                finite = self._overflow == 0         # (the head kernel raises the same flag for a non-finite confidence)
             else:
                 normed = F.normalize(feat, p=2, dim=-1)                      # :156
                 confidence = self.classify(feat)                             # :171
+                finite = torch.isfinite(confidence).all() & (self._overflow == 0)
         finally:
             torch.backends.cuda.matmul.allow_tf32 = prev_tf32
             _cabi.set_overflow_flag(None)        # (launches already made carry the pointer; nothing else may write to it)
@@ -342,5 +344,5 @@ class PointDSC(nn.Module):
             # device-side flag, no host sync: False when an operand left the range of the fp16 hi/lo split (raised by the
             # kernels at the split, include/pointdsc_b200.h pdsc_set_overflow_flag) or a confidence is not finite; the
             # numbers are then NOT to be trusted (an overflow can come back as a finite value after a ReLU)
-            "finite": torch.isfinite(confidence).all() & (self._overflow[0] == 0),
+            "finite": finite[0],
         }

@@ -1,1 +1,3 @@
-timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_forward.py -x -q -m gpu -k "dups or duplicated" -s 2>&1 | grep -v "^$" | tail -25
+bash scripts/gpu_launchlist.sh
+timeout 600 python bench.py --family kitti --n 10000 --no-config4 --no-cpu-baseline > gpurun_out/bench_final_kitti.json 2> gpurun_out/bench_final_kitti.err; echo "exit $?"; python -c "
+import json; d=json.load(open('gpurun_out/bench_final_kitti.json')); print(d['value'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['avg_launch_ms'], d['parity_check']['ok'], d['parity_check'].get('ill_conditioned_pairs'))"
