@@ -403,68 +403,113 @@ def main():
     # A timed region is EXACTLY args.steps consecutive steps between two events, measured ONCE: nothing is re-measured or
     # discarded.  Every step is also bracketed by its own events and the line reports min / median / max per step, so a
     # host-side stall inside the region (another process on the box, a page-in) is visible instead of being filtered out.
-    def timed_region(step_fn, drain_fn=None):
+    def timed_region(step_fn, drain_fn=None, n_steps=None):
+        n_steps = args.steps if n_steps is None else n_steps
         l0 = _cabi.kernel_launches()
-        marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(n_steps + 1)]
         t0 = time.perf_counter()
         marks[0].record()
-        out = None
-        for i in range(args.steps):
+        out, host_ms = None, []
+        for i in range(n_steps):
+            h0 = time.perf_counter()
             out = step_fn()
             marks[i + 1].record()
+            host_ms.append((time.perf_counter() - h0) * 1e3)
         if drain_fn is not None:
             drain_fn()                 # the last results are read inside the wall-clock region too
         barrier()
         wall = time.perf_counter() - t0
         n_launch = _cabi.kernel_launches() - l0
-        per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
-        stats = {"min": per_step[0], "median": statistics.median(per_step), "max": per_step[-1]}
+        per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(n_steps))
+        # host_enqueue_max: the longest the host spent inside one step's calls (a stall of the host shows here first)
+        stats = {"min": per_step[0], "median": statistics.median(per_step), "max": per_step[-1], "host_enqueue_max": max(host_ms)}
         return marks[0].elapsed_time(marks[-1]), wall, n_launch, stats, out
 
+    # Dress rehearsals (untimed, part of the warm-up): the whole region, run exactly as it will be timed -- the host enqueues
+    # K steps ahead of the device, which the step-by-step warm-up above never does -- for at least 1.5 s of wall clock and until
+    # two consecutive regions agree within 3 % (at most 40).  The first process on a fresh box otherwise meets one-off host
+    # stalls of up to 200 ms (page-ins from the image, driver housekeeping) inside its first asynchronous region.
+    rehearsals, prev_ms, t_reh = 0, None, time.perf_counter()
+    while rehearsals < 40:
+        cur_ms = timed_region(step_resident)[0]
+        rehearsals += 1
+        steady = prev_ms is not None and abs(cur_ms - prev_ms) <= 0.03 * min(cur_ms, prev_ms)
+        stop = torch.tensor([1.0 if steady and time.perf_counter() - t_reh >= 1.5 else 0.0], device=dev)
+        if dist is not None:
+            dist.all_reduce(stop, op=dist.ReduceOp.MIN)      # every rank runs the same number of regions (each ends in a barrier)
+        if stop.item() > 0:
+            break
+        prev_ms = cur_ms
+    attn_events.clear()
     dev_ms, t_wall, launches, step_stats, res = timed_region(step_resident)
     setattr(_cabi, attn_name, orig_attn)
     attn_ms = [a.elapsed_time(b) for a, b in attn_events]
 
     # -------- end-to-end arm (host buffers, copies inside the timed region) ----------------------
-    # A streaming caller: two sets of pinned result buffers; the results of step k are read (host waits for that step's
-    # event) after step k+1 has been enqueued, so the device never waits for the host between steps and a host-side hiccup
-    # of a few milliseconds (an NVML query of the clock sampler, a page-in) costs nothing unless it outlasts a whole step.
+    # A streaming caller: two sets of device input buffers and of pinned result buffers.  The inputs of step k+1 are copied
+    # host -> device on a second stream while step k computes (the first step of a region copies its own inputs in line);
+    # the results of step k are read (host waits for that step's event) after step k+1 has been enqueued, so the device never
+    # waits for the host between steps and a host-side hiccup of a few milliseconds (an NVML query of the clock sampler, a
+    # page-in) costs nothing unless it outlasts a whole step.  Every step's H2D, forward and D2H lie inside the timed region.
     out_trans = [torch.empty(args.pairs, 4, 4, dtype=torch.float32).pin_memory() for _ in range(2)]
     out_labels = [torch.empty(args.pairs, args.n, dtype=torch.float32).pin_memory() for _ in range(2)]
     d2h_bytes = out_trans[0].numel() * 4 + out_labels[0].numel() * 4
-    done = [None, None]            # event of the step that last wrote each buffer set
-    e2e_state = {"k": 0, "checksum": 0.0}
+    dev_in = [{k2: torch.empty_like(host[k2], device=dev) for k2 in keys} for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    in_ready = [None, None]        # event (copy stream): the inputs of that buffer set have landed
+    done = [None, None]            # event (main stream): the step that used that set has finished, results copied out
+    e2e_state = {"k": 0, "left": 0, "checksum": 0.0}
+
+    def stage_inputs(slot):
+        main = torch.cuda.current_stream()
+        copy_stream.wait_stream(main) if done[slot] is None else copy_stream.wait_event(done[slot])   # the set is free again
+        with torch.cuda.stream(copy_stream):
+            for k2 in keys:
+                dev_in[slot][k2].copy_(host[k2], non_blocking=True)
+            in_ready[slot] = torch.cuda.Event()
+            in_ready[slot].record(copy_stream)
 
     def read_results(slot):
         if done[slot] is not None:
             done[slot].synchronize()                    # the caller reads the result of that step
             e2e_state["checksum"] += float(out_trans[slot][0, 3, 3])
-            done[slot] = None
 
     def step_e2e():
         k = e2e_state["k"]
         slot = k & 1
-        read_results(slot)                              # (no-op unless the caller fell two steps behind)
         flush.zero_()
-        data = {k2: host[k2].to(dev, non_blocking=True) for k2 in keys}
+        if in_ready[slot] is None:
+            stage_inputs(slot)                          # first step of a region: nothing was staged ahead
+        torch.cuda.current_stream().wait_event(in_ready[slot])
+        in_ready[slot] = None
+        data = dict(dev_in[slot])
         data["testing"] = True
         r = model(data)
         out_trans[slot].copy_(r["final_trans"], non_blocking=True)
         out_labels[slot].copy_(r["final_labels"], non_blocking=True)
         done[slot] = torch.cuda.Event()
         done[slot].record()
-        read_results(slot ^ 1)                          # results of the previous step, while this one runs
+        e2e_state["left"] -= 1
+        if e2e_state["left"] > 0:
+            stage_inputs(slot ^ 1)                      # inputs of the next step, while this one runs
+        if k > 0:
+            read_results(slot ^ 1)                      # results of the previous step, while this one runs
         e2e_state["k"] = k + 1
         return r
 
     def drain_e2e():
-        read_results(0); read_results(1)
+        read_results((e2e_state["k"] - 1) & 1)          # the last step's results
+        torch.cuda.synchronize()
+        in_ready[0] = in_ready[1] = None
 
-    for _ in range(args.warmup):
-        step_e2e()
-    drain_e2e()
+    def run_e2e(n):
+        e2e_state["left"] = n
+        return timed_region(step_e2e, drain_e2e, n)
+
+    run_e2e(args.warmup)
+    run_e2e(args.steps)            # dress rehearsal of the region (untimed)
     barrier()
-    e2e_ms, _, _, e2e_step_stats, _ = timed_region(step_e2e, drain_e2e)
+    e2e_ms, _, _, e2e_step_stats, _ = run_e2e(args.steps)
     clocks = sampler.stop()
 
     # -------- reduce over ranks (max time) ---------------------------------------------------------
@@ -506,14 +551,16 @@ def main():
                        "N": args.n, "num_layers": NUM_LAYERS, "attn_mode": args.mode,
                        "l2": "256 MB buffer rewritten between steps (inside the timed region)",
                        "extra_warmup_steps_until_steady": settle_steps,
+                       "untimed_rehearsal_regions": rehearsals,
                        "env": {k: v for k, v in sorted(os.environ.items()) if k.startswith(("PDSC_", "POINTDSC_"))},
                        "library": os.path.basename(_cabi.LIB_PATH) + " (reads no environment variable; knobs exist only in the -DPDSC_TUNING build, which bench.py never loads)",
                        "parallelism": f"pairs sharded over {world} GPU(s), no communication"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": e2e_ms / args.steps, "step_ms": e2e_step_stats,
                     "caller": "streaming: PointDSC.forward on pinned host batches; H2D, forward and D2H of final_trans + final_labels of every "
-                              "step inside the timed region; the host reads the results of step k (event wait, two pinned buffer sets) "
-                              "after enqueueing step k+1, and the last ones before the region's closing barrier"},
+                              "step inside the timed region; the inputs of step k+1 are copied on a second stream while step k computes "
+                              "(two device input sets), the host reads the results of step k (event wait, two pinned result sets) after "
+                              "enqueueing step k+1, and the last ones before the region's closing barrier"},
             "step_ms": step_stats,
             "retimed": 0,
             "gpu_launches": launches,
