@@ -645,7 +645,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 float2 e[NP];
                 mbar_wait_role(&sm.pts_full[st], (kt >> 1) & 1, hs);
                 // (the never-taken constant branch also fences the compat block: without it ptxas spreads the
-                // compat arithmetic over the following waits and the kernel runs ~6% slower)
+                // compat arithmetic over the following waits and the kernel ran ~6% slower in round 1; re-measured in round 2
+                // against three cheaper fences -- zeros, a trap after the block, none: 0.653 vs 0.660 / 0.661 / 0.665 ms)
                 if (DBG ? (dbg & 1) : (N < 0)) {
 #pragma unroll
                     for (int i = 0; i < NP; ++i) e[i] = make_float2(0.5f, 0.25f);
