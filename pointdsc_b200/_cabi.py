@@ -192,11 +192,14 @@ def nonlocal_attn(q, k, v, src, tgt, sigma_spat, mode=ATTN_FP32, out=None, ws=No
             raise RuntimeError("q,k,v must be CUDA fp32 [B,N,C] with unit channel stride and equal row stride")
     if out is None:
         out = torch.empty(B, N, C, dtype=torch.float32, device=q.device)
+    elif not (out.is_cuda and out.dtype == torch.float32 and out.shape == q.shape and out.stride(2) == 1
+              and out.stride(0) == N * out.stride(1)):
+        raise RuntimeError("out must be CUDA fp32 [B,N,C] with unit channel stride (rows may be wider than C: a view of [B,N,ld])")
     nbytes = workspace_bytes(OP_NONLOCAL_ATTN, B, N, C, mode=mode)
     w = _ws(nbytes, q.device, ws)
     rc = lib.pdsc_nonlocal_attn(q.data_ptr(), k.data_ptr(), v.data_ptr(), q.stride(1),
                                 _ptr(src, torch.float32, "src"), _ptr(tgt, torch.float32, "tgt"),
-                                _ptr(out, torch.float32, "out"), out.stride(1), B, N, C, float(sigma_spat), int(mode),
+                                out.data_ptr(), out.stride(1), B, N, C, float(sigma_spat), int(mode),
                                 w.data_ptr(), w.numel(), _stream())
     _check(rc, "pdsc_nonlocal_attn")
     _count()

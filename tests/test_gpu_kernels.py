@@ -489,6 +489,28 @@ def test_attention_split16_vs_oracle(N, grid, mode, monkeypatch, tuning_lib):
     assert err < (5e-5 if mode == "split16" else 1e-3)
 
 
+@pytest.mark.parametrize("B,N", [(3, 1003), (1, 2500), (2, 130)])
+def test_attention_output_rows_wider_than_c(B, N):
+    """ld_out > C: the message written into a view of a wider buffer (the epilogue stores whole 128-byte pieces of rows through
+    an 8 x 8 register transpose, the stream-K combine writes the same way) is bit-identical to the contiguous result and leaves
+    the columns beside it alone; ragged N, and B = 1 with N = 2500 gives every block about eight contributors."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(77 + N)
+    C = 128
+    qkv = cu(torch.randn(B, N, 3 * C, generator=g))
+    src = cu(torch.rand(B, N, 3, generator=g))
+    tgt = cu(torch.rand(B, N, 3, generator=g))
+    ref = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=_cabi.ATTN_SPLIT16)
+    wide = torch.full((B, N, 160), 7.0, device="cuda")
+    out = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=_cabi.ATTN_SPLIT16,
+                              out=wide[:, :, 16:16 + C])
+    assert out.data_ptr() == wide[:, :, 16:].data_ptr()
+    assert torch.equal(wide[:, :, 16:16 + C], ref)
+    assert bool((wide[:, :, :16] == 7.0).all()) and bool((wide[:, :, 16 + C:] == 7.0).all())
+    exact = _cabi.nonlocal_attn(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], src, tgt, 0.1, mode=_cabi.ATTN_FP32)
+    assert float((ref - exact).abs().max()) < 5e-5
+
+
 @pytest.mark.parametrize("variant", ["cluster2", "debug_instantiation", "chain3", "chain1"])
 @pytest.mark.parametrize("grid", [None, "3"])
 @pytest.mark.parametrize("N", [100, 257, 700, 1300])
