@@ -626,6 +626,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             const int warp_row0 = (2 * rb + x) * PP_SUB + quarter * 32 + lh * 16;      // first of this warp's 16 rows in the pair
             float* out_pair = p.out + (size_t)b * N * p.ld_out;
             if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 0 + x);
+            if (si == 1) PP_TRACE(224 + warp, 1);         // rows 224..239: every softmax warp at the first boundary of the CTA
             float2 qp[6];
             {
                 const int qpr = (qrow & 63) >> 1;
@@ -656,8 +657,10 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm.pts_empty[st]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 6 + x);
+                if (si == 1 && t == 0) PP_TRACE(224 + warp, 2);
                 mbar_wait_role(&sm.s_full[x], kt & 1, hs);
                 if ((warp & 7) == 0) PP_TRACE(kt, 8 + x);
+                if (si == 1 && t == 0) PP_TRACE(224 + warp, 3);
                 tc_fence_after();
                 // e = compat * S - m  (log2 units), and its maximum over this row's keys
                 float emax = -INFINITY;
@@ -747,6 +750,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm.p_full[x]);
                 if ((warp & 7) == 0) PP_TRACE(kt, 10 + x);
+                if (si == 1 && t == 0) PP_TRACE(224 + warp, 4);
+                if (si == 0 && t == n - 1) PP_TRACE(224 + warp, 7);
             }
                 if (CHAIN && t < n) {
                     // Chain limit: the finished chain's O and its reference max go to this thread's slot of the workspace (stores
@@ -775,6 +780,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
             mbar_wait_role(&sm.pv_done[x], (kt - 1) & 1, hs);
             tc_fence_after();
             if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 4 + x);
+            if (si == 0) PP_TRACE(224 + warp, 5);
             // O of the segment = the last chain (TMEM) + the finished chains (workspace slots, each relative to the reference
             // max it was stored with)
             const int nflush = CHAIN ? (n - 1) / p.chain : 0;
@@ -914,6 +920,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) attn_pp_kernel(const PpParams p
                 }
             }
             if ((warp & 7) == 0) PP_TRACE(240 + min(si, 15), 6 + x);
+            if (si == 0) PP_TRACE(224 + warp, 0);
             s = s_next;
             have = have_next;
         }
@@ -1097,9 +1104,15 @@ int launch_attn_pp_main(float* out, int64_t ld_out, int B, int N, int C, int mod
         cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
         if (FILE* f = fopen(trace_path, "w")) {
             fprintf(f, "# step kIssued vIssued pfullA pfullB issuedA issuedB compatA compatB sSeenA sSeenB pArrA pArrB vfull kfullNext (clocks relative to step 0 kIssued)\n");
-            for (int i = 0; i < 240 && h[i * 16]; ++i) {
+            for (int i = 0; i < 224 && h[i * 16]; ++i) {
                 fprintf(f, "%d", i);
                 for (int e = 0; e < 14; ++e) fprintf(f, " %lld", h[i * 16 + e] ? h[i * 16 + e] - h[0] : -1);
+                fprintf(f, "\n");
+            }
+            fprintf(f, "# per warp at the first boundary: epilogue done | next segment entered | Q_hi + first compat done | S seen | P handed over | last PV seen | - | last P of segment 0 handed over\n");
+            for (int i = 224; i < 240; ++i) {
+                fprintf(f, "# warp %d", i - 224);
+                for (int e = 0; e < 8; ++e) fprintf(f, " %lld", h[i * 16 + e] ? h[i * 16 + e] - h[0] : -1);
                 fprintf(f, "\n");
             }
             fprintf(f, "# segment startA startB bodyDoneA bodyDoneB lastPvA lastPvB epiDoneA epiDoneB\n");
