@@ -108,13 +108,25 @@ int pdsc_split16_rows(const float* x, const float* add, float* y_out, void* out1
  *  (fp32-grade accuracy), one 128-row tile kept on chip through the whole chain.
  *  x, add_in (nullable): fp32 [rows, dims[0]]; add_out (nullable), y_out (nullable): fp32 [rows, dims[n_layers]];
  *  y_packed (nullable): fp16 [rows, Kp] in the pdsc_split16_rows row layout (operand of a following library GEMM).
- *  dims (n_layers + 1 entries, each 64 or 128) and relu (n_layers flags) are HOST arrays; n_layers <= 3.
+ *  dims (n_layers + 1 entries, each 64 or 128) and relu (n_layers flags) are HOST arrays; n_layers <= 3 (shared-memory staging of the rows; pdsc_mlp_chain_direct takes 4).
  *  wpack (device): per layer the tcgen05 B-operand image of W_i (BatchNorm folded): fp16 hi then fp16 lo, each
  *  dims[i]/64 blocks of [dims[i+1] rows x 64 input channels], 128-byte rows with the 128B swizzle (16-byte chunk c of
  *  row r stored at chunk c ^ (r & 7)).  bias (device): the b_i concatenated, fp32. */
 int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_layers, const int32_t* dims,
                    const int32_t* relu, const void* wpack, const float* bias, const float* add_out,
                    float* y_out, void* y_packed, int Kp, void* stream);
+
+/* The same chain with up to FOUR layers and the residual added after any layer:
+ *      y = L_{n-1}( .. L_{r+1}( L_r( .. L_0(x) .. ) + residual ) .. ),   r = residual_layer (ignored when residual is NULL),
+ *  which is fc_message + residual of one encoder layer followed by the PointCN of the next (NonLocalBlock.forward
+ *  models/PointDSC.py:12-18,44, then PointCN :54-62) in one launch: the sum feat + fc_message(msg) is consumed on chip
+ *  and never written.  Same arithmetic, term by term, as two pdsc_mlp_chain calls (results are bit-identical).
+ *  x: fp32 [rows, dims[0]]; residual: fp32 [rows, dims[residual_layer + 1]]; y_out: fp32 [rows, dims[n_layers]];
+ *  dims, relu, wpack, bias as for pdsc_mlp_chain; n_layers <= 4.  Rows move straight between global memory and registers
+ *  (shared memory holds the weights only). */
+int pdsc_mlp_chain_direct(const float* x, int64_t rows, int n_layers, const int32_t* dims, const int32_t* relu,
+                          const void* wpack, const float* bias, const float* residual, int residual_layer,
+                          float* y_out, void* stream);
 
 /* (c) NMS seed picking; replaces PointDSC.pick_seeds models/PointDSC.py:199-217.
  *  is_local_max[i] = all_j (score_i >= score_j  or  |s_i-s_j| >= R);

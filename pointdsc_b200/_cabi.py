@@ -56,6 +56,8 @@ SIGNATURES = {
     "pdsc_classification_counts": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pdsc_mlp_chain": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_int, c_void_p]),
+    "pdsc_mlp_chain_direct": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                      c_void_p, c_void_p]),
     "pdsc_compat_matvec": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                    c_void_p, c_void_p]),
     "pdsc_power_normalize": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -297,6 +299,24 @@ def mlp_chain(x, chain, add_in=None, add_out=None, want_y=True, want_packed=Fals
     _check(rc, "pdsc_mlp_chain")
     _count()
     return y, yp
+
+
+def mlp_chain_direct(x, chain, residual=None, residual_layer=0):
+    """y = chain(x) with `residual` added to the output of layer `residual_layer` (0-based) before the next layer; up to four
+    layers, rows straight between global memory and registers (pdsc_mlp_chain_direct)."""
+    lib = load()
+    rows, K = x.shape
+    assert K == chain.dims[0]
+    if residual is not None:
+        assert residual.shape == (rows, chain.dims[residual_layer + 1])
+    y = torch.empty(rows, chain.dims[-1], dtype=torch.float32, device=x.device)
+    rc = lib.pdsc_mlp_chain_direct(_ptr(x, torch.float32, "x"), rows, len(chain.relu), ctypes.cast(chain.c_dims, c_void_p),
+                                   ctypes.cast(chain.c_relu, c_void_p), _ptr(chain.wpack, torch.uint8, "wpack"),
+                                   _ptr(chain.bias, torch.float32, "bias"), _ptr(residual, torch.float32, "residual"),
+                                   int(residual_layer), _ptr(y), _stream())
+    _check(rc, "pdsc_mlp_chain_direct")
+    _count()
+    return y
 
 
 def pick_seeds(src, scores, R, S, ws=None, want_aux=False):

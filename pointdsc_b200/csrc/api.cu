@@ -180,6 +180,16 @@ int pdsc_mlp_chain(const float* x, const float* add_in, int64_t rows, int n_laye
                             reinterpret_cast<cudaStream_t>(stream));
 }
 
+int pdsc_mlp_chain_direct(const float* x, int64_t rows, int n_layers, const int32_t* dims, const int32_t* relu, const void* wpack,
+                          const float* bias, const float* residual, int residual_layer, float* y_out, void* stream) {
+    PDSC_REQUIRE(x && dims && relu && wpack && bias && y_out, "mlp_chain_direct: null pointer");
+    PDSC_REQUIRE(rows > 0, "mlp_chain_direct: rows must be positive");
+    PDSC_REQUIRE(aligned16(x) && aligned16(wpack) && aligned16(y_out) && (!residual || aligned16(residual)),
+                 "mlp_chain_direct: pointers must be 16-byte aligned");
+    return launch_mlp_chain_direct(x, rows, n_layers, dims, relu, wpack, bias, residual, residual_layer, y_out,
+                                   reinterpret_cast<cudaStream_t>(stream));
+}
+
 int pdsc_pick_seeds(const float* src, const float* scores, int B, int N, float R, int S, int64_t* seeds_out,
                     uint8_t* is_local_max_out, int32_t* n_pos_out, void* ws, size_t ws_bytes, void* stream) {
     PDSC_REQUIRE(src && scores && seeds_out && ws, "pick_seeds: null pointer");

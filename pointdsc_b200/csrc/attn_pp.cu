@@ -384,22 +384,7 @@ __device__ __forceinline__ uint32_t pp_priv_index(int w8, int f, int lane) { ret
 // In-register transpose of an 8 x 8 matrix of float4 over the 8 lanes of a group (k = lane & 7): before, lane k holds the
 // eight float4 of ITS 128-byte piece; after, it holds float4 number k of the pieces of the lanes 8g .. 8g+7.  A warp store of
 // element j then writes four whole 128-byte lines (one per group) instead of 16 bytes into each of 32 lines.
-__device__ __forceinline__ void pp_transpose8(uint32_t (&r)[32], int k) {
-#pragma unroll
-    for (int m = 1; m < 8; m <<= 1) {
-        const bool up = (k & m) != 0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (j & m) continue;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const uint32_t a = r[4 * j + q], b = r[4 * (j | m) + q];
-                const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, m);
-                if (up) r[4 * j + q] = got; else r[4 * (j | m) + q] = got;
-            }
-        }
-    }
-}
+__device__ __forceinline__ void pp_transpose8(uint32_t (&r)[32], int k) { warp_transpose8(r, k); }      // (sm100.cuh)
 
 // Rows of the output: chunk c (32 channels) of the 64 channels every lane of the warp owns, already scaled.  `tile_row0` =
 // first row of the warp's 16 rows in the pair, lanes 0-15 own channels [0,64) of those rows and lanes 16-31 channels [64,128).

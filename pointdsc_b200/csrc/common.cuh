@@ -268,6 +268,8 @@ int launch_split16_rows(const float* x, const float* add, float* y_out, void* ou
 int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_layers, const int32_t* dims,
                      const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y,
                      void* y_packed, int Kp, cudaStream_t st);
+int launch_mlp_chain_direct(const float* x, long long rows, int n_layers, const int32_t* dims, const int32_t* relu, const void* wpack,
+                            const float* bias, const float* res, int res_layer, float* y, cudaStream_t st);
 size_t power_workspace(int N);
 size_t power_p2p_exchange_bytes(int N);
 int launch_compat_matvec_p2p(const float* src, const float* tgt, const float* v, int N, int row_begin, int row_end,

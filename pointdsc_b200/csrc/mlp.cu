@@ -18,7 +18,10 @@ namespace pdsc {
 
 using namespace sm100;
 
-constexpr int ML_MAX_LAYERS = 3;
+constexpr int ML_MAX_LAYERS = 4;
+#ifndef ML_DIRECT_GROUPS
+#define ML_DIRECT_GROUPS 2
+#endif
 constexpr int ML_THREADS = 256;     // two threads per row: thread t and t + 128 share row t & 127 and take alternate 32-column chunks
 constexpr uint32_t ML_A_LO = 64;      // TMEM columns: A hi [0,64), A lo [64,128), D [128,256)
 constexpr uint32_t ML_D = 128;
@@ -35,6 +38,7 @@ struct MlpParams {
     uint32_t w_bytes, n_bias;
     int Kp;                            // row length (halves) of the packed output
     int32_t* overflow;                 // caller's operand-range flag (common.cuh), may be null
+    const float* res; int res_layer;   // mlp_chain_direct_kernel: residual [rows, N[res_layer]] added to the output of that layer
 };
 
 __device__ __forceinline__ uint64_t ml_uniform64(uint64_t v) {   // broadcast from lane 0: provably warp-uniform
@@ -256,6 +260,187 @@ __global__ void __launch_bounds__(ML_THREADS, 1) mlp_chain_kernel(const MlpParam
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same chain with the rows moved straight between global memory and registers, shared memory = weights only, so that a
+// chain of four layers fits: fc_message + residual of one encoder layer AND the PointCN of the next in one launch
+// (models/PointDSC.py:12-18,44 then :54-62) -- the sum  feat + fc_message(msg)  is consumed on chip and never written.
+//     x -> L_0 .. L_{r} (+ res) -> L_{r+1} .. L_{n-1} -> y
+// A thread still owns one 128-byte piece (32 channels) of a row at a time, which as a plain load would touch 32 lines per
+// warp instruction (round 1 measured that: slower than staging).  Here the eight lanes of a group read ONE whole line per
+// instruction -- lane k the k-th float4 of the row of lane 8g + j in instruction j -- and an 8 x 8 register transpose
+// (warp_transpose8) hands every lane its own piece; stores go the other way round.
+__device__ __forceinline__ void ml_load_piece(const float* src, int width, long long row0, long long rows, int c, int lane, uint32_t (&r)[32]) {
+    const int g8 = lane & ~7, k = lane & 7;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const long long row = min(row0 + g8 + j, rows - 1);
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + row * width + c * 32) + k);
+        r[4 * j] = v.x; r[4 * j + 1] = v.y; r[4 * j + 2] = v.z; r[4 * j + 3] = v.w;
+    }
+}
+__device__ __forceinline__ void ml_store_piece(float* dst, int width, long long row0, long long rows, int c, int lane, uint32_t (&r)[32]) {
+    const int g8 = lane & ~7, k = lane & 7;
+    warp_transpose8(r, k);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const long long row = row0 + g8 + j;
+        if (row < rows)
+            *(reinterpret_cast<uint4*>(dst + row * width + c * 32) + k) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+    }
+}
+
+// GROUPS = 1: 8 warps, the next tile's input pieces and this tile's residual pieces are fetched into registers ahead of use
+// (255 registers).  GROUPS = 2: two independent 8-warp groups per CTA, each walking its own tiles with its own 256 TMEM
+// columns and the weights shared in shared memory; no register prefetch (128 registers) -- while one group waits for a
+// load, an MMA or a barrier the other one runs.
+template <int GROUPS>
+__global__ void __launch_bounds__(ML_THREADS * GROUPS, 1) mlp_chain_direct_kernel(const MlpParams p) {
+    constexpr bool PREFETCH = GROUPS == 1;
+    uint32_t bad = 0;                                       // operand-range test of every split (common.cuh)
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* wsm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* bsm = reinterpret_cast<float*>(wsm + p.w_bytes);
+    __shared__ uint64_t w_bar, mma_bar[GROUPS];
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int gi = threadIdx.x / ML_THREADS, gt = threadIdx.x % ML_THREADS;      // group, thread inside the group
+    auto group_sync = [&]() { if (GROUPS == 1) __syncthreads(); else named_bar_sync(1 + gi, ML_THREADS); };
+
+    if (threadIdx.x == 0) {
+        mbar_init(&w_bar, 1);
+        for (int i = 0; i < GROUPS; ++i) mbar_init(&mma_bar[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 256 * GROUPS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s + 256u * gi;
+    const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;      // a warp reaches the TMEM lanes of its quadrant (warp % 4)
+    const int half = gt >> 7;                                          // which 32-channel pieces of its row this thread takes
+    const int wrow0 = (warp & 3) * 32;                                 // first row of the tile this warp's lanes own
+    const int k8 = lane & 7;
+    const long long n_tiles = (p.rows + 127) / 128;
+    const long long tile0 = (long long)blockIdx.x * GROUPS + gi, tile_step = (long long)gridDim.x * GROUPS;
+    const int K0 = p.K[0], NL = p.N[p.n_layers - 1], NR = p.N[p.res_layer];
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&w_bar, p.w_bytes);
+        for (uint32_t off = 0; off < p.w_bytes; off += 32768u) {
+            const uint32_t n = min(32768u, p.w_bytes - off);
+            bulk_g2s(wsm + off, p.wpack + off, n, &w_bar);
+        }
+    }
+    // pieces c = half, half + 2 of the first tile's rows (in flight while the weights arrive)
+    uint32_t xin[2][32], rin[2][32];
+    if (PREFETCH && tile0 < n_tiles) {
+#pragma unroll
+        for (int ci = 0; ci < 2; ++ci)
+            if (half + 2 * ci < K0 / 32) ml_load_piece(p.x, K0, tile0 * 128 + wrow0, p.rows, half + 2 * ci, lane, xin[ci]);
+    }
+    for (uint32_t i = threadIdx.x; i < p.n_bias; i += ML_THREADS * GROUPS) bsm[i] = p.bias[i];
+    __syncthreads();
+    mbar_wait_role(&w_bar, 0);
+
+    uint32_t mma_phase = 0;
+    for (long long tile = tile0; tile < n_tiles; tile += tile_step) {
+        const long long row0 = tile * 128 + wrow0;
+        const long long next = tile + tile_step;
+        // ---- input pieces -> A operand (hi, lo) in TMEM ----
+#pragma unroll
+        for (int ci = 0; ci < 2; ++ci) {
+            const int c = half + 2 * ci;
+            if (c < K0 / 32) {
+                if (!PREFETCH) ml_load_piece(p.x, K0, row0, p.rows, c, lane, xin[ci]);
+                warp_transpose8(xin[ci], k8);
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    ml_split_pair(__uint_as_float(xin[ci][2 * i]), __uint_as_float(xin[ci][2 * i + 1]), hi[i], lo[i], bad);
+                tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
+                tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
+            }
+        }
+        if (PREFETCH) {
+            // the residual pieces of this tile and the input pieces of the next one fly while the chain runs
+#pragma unroll
+            for (int ci = 0; ci < 2; ++ci) {
+                if (p.res && half + 2 * ci < NR / 32) ml_load_piece(p.res, NR, row0, p.rows, half + 2 * ci, lane, rin[ci]);
+                if (next < n_tiles && half + 2 * ci < K0 / 32) ml_load_piece(p.x, K0, next * 128 + wrow0, p.rows, half + 2 * ci, lane, xin[ci]);
+            }
+        }
+        for (int l = 0; l < p.n_layers; ++l) {
+            const int K = p.K[l], N = p.N[l];
+            tmem_st_wait();
+            tc_fence_before();
+            group_sync();              // every row's A operand is in TMEM, and everyone is done reading D
+            if ((warp & 7) == 0) {
+                tc_fence_after();
+                const uint32_t idesc = umma_idesc_f16(128, N);
+                const uint32_t blk = (uint32_t)N * 128u;                  // bytes of one 64-channel B block
+                const uint32_t lo_off = (uint32_t)(K / 64) * blk;         // lo image follows the hi image
+                const uint64_t wd = ml_uniform64(umma_desc_sw128_kmajor(smem_u32(wsm + p.w_off[l])));
+                uint32_t acc = 0;
+                for (int ti = 0; ti < 3; ++ti) {                          // cross terms first (see mlp_chain_kernel)
+                    const int term = ti == 2 ? 0 : ti + 1;
+                    const uint32_t a0 = tmem + (term == 2 ? ML_A_LO : 0u);
+                    const uint32_t b0 = term == 1 ? lo_off : 0u;
+                    for (int kk = 0; kk < K / 16; ++kk) {
+                        const uint64_t db = wd + (uint64_t)((b0 + (uint32_t)(kk >> 2) * blk + (uint32_t)(kk & 3) * 32u) >> 4);
+                        umma_ts_elect(tmem + ML_D, a0 + (uint32_t)kk * 8u, db, idesc, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit_elect(&mma_bar[gi]);
+            }
+            const bool last = l + 1 == p.n_layers;
+            const bool add_res = p.res && l == p.res_layer;
+            if (!PREFETCH && add_res) {
+#pragma unroll
+                for (int ci = 0; ci < 2; ++ci)
+                    if (half + 2 * ci < N / 32) ml_load_piece(p.res, NR, row0, p.rows, half + 2 * ci, lane, rin[ci]);     // (lands while the MMAs run)
+            }
+            mbar_wait(&mma_bar[gi], mma_phase);
+            mma_phase ^= 1;
+            tc_fence_after();
+            const float* bias = bsm + p.b_off[l];
+#pragma unroll
+            for (int ci = 0; ci < 2; ++ci) {
+                const int c = half + 2 * ci;
+                if (c >= N / 32) continue;
+                uint32_t r[32];
+                tmem_ld32(tmem + lane_addr + ML_D + (uint32_t)c * 32u, r);
+                tmem_ld_wait();
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    v[i] = __uint_as_float(r[i]) + bias[c * 32 + i];
+                    if (p.relu[l]) v[i] = fmaxf(v[i], 0.f);
+                }
+                if (add_res) {
+                    warp_transpose8(rin[ci], k8);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(rin[ci][i]);
+                }
+                if (!last) {
+                    uint32_t hi[16], lo[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ml_split_pair(v[2 * i], v[2 * i + 1], hi[i], lo[i], bad);
+                    tmem_st16(tmem + lane_addr + (uint32_t)c * 16u, hi);
+                    tmem_st16(tmem + lane_addr + ML_A_LO + (uint32_t)c * 16u, lo);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+                    ml_store_piece(p.y, NL, row0, p.rows, c, lane, r);
+                }
+            }
+        }
+    }
+    if (bad && p.overflow) atomicOr(p.overflow, 1);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base_s, 256 * GROUPS);
+}
+
 int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_layers, const int32_t* dims,
                      const int32_t* relu, const void* wpack, const float* bias, const float* add_out, float* y,
                      void* y_packed, int Kp, cudaStream_t st) {
@@ -264,6 +449,7 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     p.x = x; p.add_in = add_in; p.add_out = add_out; p.y = y; p.y_packed = reinterpret_cast<uint8_t*>(y_packed);
     p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.rows = rows; p.n_layers = n_layers; p.Kp = Kp;
     p.overflow = overflow_flag();
+    p.res = nullptr; p.res_layer = 0;
     uint32_t woff = 0, boff = 0;
     for (int l = 0; l < n_layers; ++l) {
         const int K = dims[l], N = dims[l + 1];
@@ -286,6 +472,42 @@ int launch_mlp_chain(const float* x, const float* add_in, long long rows, int n_
     mlp_chain_kernel<<<(int)grid, ML_THREADS, smem, st>>>(p);
     count_launches(1);
     return check_launch("mlp_chain");
+}
+
+int launch_mlp_chain_direct(const float* x, long long rows, int n_layers, const int32_t* dims, const int32_t* relu, const void* wpack,
+                            const float* bias, const float* res, int res_layer, float* y, cudaStream_t st) {
+    if (n_layers < 1 || n_layers > ML_MAX_LAYERS) { set_error("mlp_chain_direct: 1..%d layers supported", ML_MAX_LAYERS); return PDSC_ERR_ARG; }
+    if (res && (res_layer < 0 || res_layer >= n_layers)) { set_error("mlp_chain_direct: residual layer %d outside the chain", res_layer); return PDSC_ERR_ARG; }
+    MlpParams p;
+    p.x = x; p.add_in = nullptr; p.add_out = nullptr; p.y = y; p.y_packed = nullptr; p.Kp = 0;
+    p.wpack = reinterpret_cast<const uint8_t*>(wpack); p.bias = bias; p.rows = rows; p.n_layers = n_layers;
+    p.res = res; p.res_layer = res ? res_layer : 0;
+    p.overflow = overflow_flag();
+    uint32_t woff = 0, boff = 0;
+    for (int l = 0; l < n_layers; ++l) {
+        const int K = dims[l], N = dims[l + 1];
+        if ((K != 64 && K != 128) || (N != 64 && N != 128)) { set_error("mlp_chain_direct: layer dims must be 64 or 128 (got %d -> %d)", K, N); return PDSC_ERR_ARG; }
+        p.K[l] = K; p.N[l] = N; p.relu[l] = relu[l];
+        p.w_off[l] = woff; p.b_off[l] = boff;
+        woff += 2u * (uint32_t)(K / 64) * (uint32_t)N * 128u;
+        boff += (uint32_t)N;
+    }
+    p.w_bytes = woff; p.n_bias = boff;
+    const int smem = (int)(p.w_bytes + p.n_bias * sizeof(float) + 1024);       // weights | biases
+    if (smem > 227 * 1024) { set_error("mlp_chain_direct: weights do not fit in shared memory (%d bytes)", smem); return PDSC_ERR_ARG; }
+    const long long n_tiles = (rows + 127) / 128;
+    long long grid = num_sms();
+    const int groups = (ML_DIRECT_GROUPS == 2 && n_tiles >= 2 * grid) ? 2 : 1;      // two tiles in flight per SM when there are enough
+    if (groups == 2) {
+        opt_in_smem<mlp_chain_direct_kernel<2>>(smem);
+        mlp_chain_direct_kernel<2><<<(int)grid, ML_THREADS * 2, smem, st>>>(p);
+    } else {
+        if (grid > n_tiles) grid = n_tiles;
+        opt_in_smem<mlp_chain_direct_kernel<1>>(smem);
+        mlp_chain_direct_kernel<1><<<(int)grid, ML_THREADS, smem, st>>>(p);
+    }
+    count_launches(1);
+    return check_launch("mlp_chain_direct");
 }
 
 }  // namespace pdsc

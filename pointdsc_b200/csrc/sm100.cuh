@@ -78,6 +78,27 @@ __device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity
         : "memory");
 }
 
+// ---- in-register 8 x 8 transpose of float4 over the 8 lanes of a group -------------------------------
+// k = lane & 7.  Before: lane k holds eight float4 (r[4j .. 4j+3], j = 0..7); after: r[4j ..] = element k of what lane
+// (lane & ~7) + j held.  Used to turn "one 128-byte piece of a row per thread" (32 lines per warp load / store) into
+// "eight lanes per 128-byte line" (4 whole lines per warp instruction) and back: 48 shuffles per 32 registers.
+__device__ __forceinline__ void warp_transpose8(uint32_t (&r)[32], int k) {
+#pragma unroll
+    for (int m = 1; m < 8; m <<= 1) {
+        const bool up = (k & m) != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (j & m) continue;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t a = r[4 * j + q], b = r[4 * (j | m) + q];
+                const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, m);
+                if (up) r[4 * j + q] = got; else r[4 * (j | m) + q] = got;
+            }
+        }
+    }
+}
+
 // ---- bulk async copy global -> shared (TMA engine, no tensor map) ----------------------------------
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

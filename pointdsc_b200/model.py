@@ -129,6 +129,9 @@ class PointDSC(nn.Module):
         # "split16" = every layer a library GEMM on packed fp16 hi/lo operands (torch.mm, fp32 accumulation/output);
         # "fp32" = plain fp32 addmm.  All three are fp32-grade accurate.
         self.mlp_mode = os.environ.get("POINTDSC_MLP_MODE", "fused")
+        # fused mode: fc_message + residual of a layer and the next layer's PointCN in one launch (False: two launches,
+        # the round-1 form; results are bit-identical either way)
+        self.join_layers = os.environ.get("POINTDSC_JOIN_LAYERS", "1") != "0"
         if self.mlp_mode not in _MLP_MODES:
             raise ValueError(f"POINTDSC_MLP_MODE={self.mlp_mode!r}: expected one of {_MLP_MODES}")
         self._packed = None
@@ -182,6 +185,11 @@ class PointDSC(nn.Module):
                     L["qkv_b"] = torch.cat([bq, bk, bv]).float().contiguous()
             layers.append(L)
         P["layers"] = layers
+        if self.num_channels == 128:
+            # fc_message + residual of layer i and the PointCN of layer i+1 as ONE chain (pdsc_mlp_chain_direct): the sum
+            # feat + fc_message(msg) never leaves the chip
+            for L, nxt in zip(layers[:-1], layers[1:]):
+                L["join_chain"] = _cabi.MlpChain([L["m0"], L["m3"], L["m6"], nxt["pcn"]], [True, True, False, True])
         P["cls"] = [_fold(self.classification[i], None) for i in (0, 2, 4)]
         P["cls"] = [(W.contiguous(), b.contiguous()) for W, b in P["cls"]]
         P["cls_w3"] = P["cls"][2][0].reshape(-1).contiguous()
@@ -239,8 +247,9 @@ class PointDSC(nn.Module):
         return feat.view(B, N, C)
 
     def _encode_fused(self, P, feat, src, tgt, B, N, C):
-        """Per layer four kernels, all hand-written: PointCN (pdsc_mlp_chain), q/k/v projection straight into the
-        attention operand tiles (pdsc_qkv_pack), the attention itself, fc_message + residual (pdsc_mlp_chain)."""
+        """Per layer three kernels, all hand-written: q/k/v projection straight into the attention operand tiles
+        (pdsc_qkv_pack), the attention itself, and fc_message + residual joined with the NEXT layer's PointCN
+        (pdsc_mlp_chain_direct); the first PointCN and the last fc_message + residual are pdsc_mlp_chain launches."""
         x = feat
         if self.attn_mode == _cabi.ATTN_FP32:
             for L in P["layers"]:
@@ -250,12 +259,19 @@ class PointDSC(nn.Module):
                                           P["sigma_spat"], mode=self.attn_mode, ws=self._ws)
                 x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)
             return x.view(B, N, C)
-        for L in P["layers"]:
-            y1, _ = _cabi.mlp_chain(x, L["pcn_chain"])                                      # PointCN conv+BN+ReLU
+        y1, _ = _cabi.mlp_chain(x, P["layers"][0]["pcn_chain"])                             # PointCN conv+BN+ReLU
+        layers = P["layers"]
+        for i, L in enumerate(layers):
             w = _cabi.qkv_pack(y1.view(B, N, C), L["qkv_w"], L["qkv_b"], src, tgt, P["sigma_spat"], ws=self._ws,
                                mode=self.attn_mode)
             msg = _cabi.nonlocal_attn_packed(w, B, N, C, mode=self.attn_mode)
-            x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)          # feat + fc_message(msg)
+            if self.join_layers and "join_chain" in L:
+                # feat + fc_message(msg), then the next layer's PointCN, in one launch (the sum stays on chip)
+                y1 = _cabi.mlp_chain_direct(msg.view(B * N, C), L["join_chain"], residual=y1, residual_layer=2)
+            else:
+                x, _ = _cabi.mlp_chain(msg.view(B * N, C), L["msg_chain"], add_out=y1)      # feat + fc_message(msg)
+                if i + 1 < len(layers):
+                    y1, _ = _cabi.mlp_chain(x, layers[i + 1]["pcn_chain"])                  # the next PointCN
         return x.view(B, N, C)
 
     def _encode_split16(self, P, feat, src, tgt, B, N, C):

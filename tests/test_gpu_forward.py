@@ -99,6 +99,21 @@ def test_forward_vs_reference_golden_at_full_size(case, mode):
                             pair["tgt_keypts"][0], thr)
 
 
+def test_joined_layer_chains_change_nothing():
+    """model.join_layers (fc_message + residual of a layer and the next PointCN in one pdsc_mlp_chain_direct launch, the default)
+    against the two-launch form: every output bit-identical."""
+    meta, g = load_golden("g1_3dmatch_n1000_l12")
+    model, _ = golden_model(meta)
+    data = {k: g[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+    data["testing"] = True
+    assert model.join_layers
+    a = model(data)
+    model.join_layers = False
+    b = model(data)
+    for k in ("confidence", "seeds", "inlier_count", "initial_trans", "final_trans", "final_labels", "corr_features"):
+        assert torch.equal(a[k], b[k]), k
+
+
 def test_batched_forward_equals_per_pair_runs():
     """[B,N,.] means B independent pairs (reference test path is batch-size 1)."""
     meta, g = load_golden("g0_3dmatch_n256_l2")

@@ -175,6 +175,41 @@ def test_feature_head_vs_torch(B, N):
     assert bool((normed[0, 0] == 0).all())
 
 
+@pytest.mark.parametrize("rows", [16 * 5000, 1003, 128, 37])
+def test_mlp_chain_direct_equals_two_chains(rows):
+    """pdsc_mlp_chain_direct on [fc_message (128-64-64-128) + residual, PointCN (128-128, ReLU)] -- what the encoder runs between
+    two attention launches -- against the two pdsc_mlp_chain launches it replaces: bit-identical (same arithmetic, the sum
+    just never leaves the chip), and against fp64 torch within the split's accuracy; ragged tile at the end."""
+    from pointdsc_b200 import _cabi
+    g = torch.Generator().manual_seed(rows)
+    def lin(k, n):
+        return (torch.randn(k, n, generator=g) / k ** 0.5).cuda(), (0.1 * torch.randn(n, generator=g)).cuda()
+    m0, m3, m6, pcn = lin(128, 64), lin(64, 64), lin(64, 128), lin(128, 128)
+    msg = cu(torch.randn(rows, 128, generator=g))
+    y1 = cu(torch.randn(rows, 128, generator=g))
+    msg_chain = _cabi.MlpChain([m0, m3, m6], [True, True, False])
+    pcn_chain = _cabi.MlpChain([pcn], [True])
+    join = _cabi.MlpChain([m0, m3, m6, pcn], [True, True, False, True])
+    x, _ = _cabi.mlp_chain(msg, msg_chain, add_out=y1)
+    ref, _ = _cabi.mlp_chain(x, pcn_chain)
+    out = _cabi.mlp_chain_direct(msg, join, residual=y1, residual_layer=2)
+    assert torch.equal(out, ref)
+    d = msg.double()
+    for (W, b), relu in zip((m0, m3, m6), (True, True, False)):
+        d = d @ W.double() + b.double()
+        d = d.clamp_min(0) if relu else d
+    d = ((d + y1.double()) @ pcn[0].double() + pcn[1].double()).clamp_min(0)
+    assert float((out.double() - d).abs().max()) < 2e-5 * max(1.0, float(d.abs().max()))
+    # without a residual, and with it after the first layer
+    two = _cabi.MlpChain([m0, m3], [True, False])
+    a, _ = _cabi.mlp_chain(msg, two)
+    assert torch.equal(_cabi.mlp_chain_direct(msg, two), a)
+    r64 = cu(torch.randn(rows, 64, generator=g))
+    first, _ = _cabi.mlp_chain(msg, _cabi.MlpChain([m0], [True]), add_out=r64)
+    b2, _ = _cabi.mlp_chain(first, _cabi.MlpChain([m3], [False]))
+    assert torch.equal(_cabi.mlp_chain_direct(msg, two, residual=r64, residual_layer=0), b2)
+
+
 # --------------------------------------------------------------------------------- (c) seed kNN
 @pytest.mark.parametrize("case", GOLDEN_CASES)
 def test_seed_knn_vs_reference_golden(case):
