@@ -239,7 +239,11 @@ __global__ void fill_ones_kernel(float* v, int N, int32_t* flag, int32_t* iters)
 //     6      1614      833      443      258
 //     8      1624      826      446      235      <- 86 % of 1624 / 8 on 1/8 of the rows
 // (a wave model -- 4 resident CTAs per SM, 6 x 98 clusters = one wave -- predicted 6; the 8-GPU run said 2.95 ms against
-// 2.76 ms with 8.)  PDSC_MV_KS (tuning build) overrides it.
+// 2.76 ms with 8.)  Non-portable cluster sizes, measured later on another box (8 there: 1645 / 848 / 455 / 243):
+//    10      1591      808      416      244
+//    12      1798      921      478      259
+//    16      1863      950      497      264      <- larger clusters schedule worse; nothing beats 8 on 1/8 of the rows
+// PDSC_MV_KS (tuning build) overrides it (up to 8).
 static int mv_column_splits(int N) {
     (void)N;
     const int knob = tuning_int("PDSC_MV_KS", 0);
