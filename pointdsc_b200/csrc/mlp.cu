@@ -292,7 +292,8 @@ __device__ __forceinline__ void ml_store_piece(float* dst, int width, long long 
 // GROUPS = 1: 8 warps, the next tile's input pieces and this tile's residual pieces are fetched into registers ahead of use
 // (255 registers).  GROUPS = 2: two independent 8-warp groups per CTA, each walking its own tiles with its own 256 TMEM
 // columns and the weights shared in shared memory; no register prefetch (128 registers) -- while one group waits for a
-// load, an MMA or a barrier the other one runs.
+// load, an MMA or a barrier the other one runs.  (prefetch.global.L2 of the next tile's input and this tile's residual at the
+// top of a tile was measured: 9.976 vs 9.963 ms per forward at 16 x N=5000, 3.632 vs 3.602 at 64 x N=1000 -- not kept.)
 template <int GROUPS>
 __global__ void __launch_bounds__(ML_THREADS * GROUPS, 1) mlp_chain_direct_kernel(const MlpParams p) {
     constexpr bool PREFETCH = GROUPS == 1;
