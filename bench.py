@@ -523,8 +523,15 @@ def main():
     clocks = sampler.stop()
 
     # -------- reduce over ranks (max time) ---------------------------------------------------------
-    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([dev_ms, e2e_ms, step_stats["max"], step_stats["host_enqueue_max"]], dtype=torch.float64, device=dev)
+    per_rank = None
     if dist is not None:
+        every = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(every, t)
+        # what each rank measured (the line's times are the maxima): a slow rank -- a GPU with a lower power cap, a host stall
+        # on one process -- is visible instead of only lowering the aggregate
+        per_rank = {"region_ms": [float(x[0]) for x in every], "e2e_region_ms": [float(x[1]) for x in every],
+                    "step_ms_max": [float(x[2]) for x in every], "host_enqueue_max": [float(x[3]) for x in every]}
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
     total_pairs = args.pairs * world * args.steps
@@ -573,6 +580,7 @@ def main():
                               "(two device input sets), the host reads the results of step k (event wait, two pinned result sets) after "
                               "enqueueing step k+1, and the last ones before the region's closing barrier"},
             "step_ms": step_stats,
+            "per_rank": per_rank,
             "retimed": 0,
             "gpu_launches": launches,
             "clocks": clocks,
