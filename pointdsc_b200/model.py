@@ -6,9 +6,11 @@ contract (:128-197), so ``model.load_state_dict(torch.load('model_best.pkl'))`` 
 ``res = model(data)`` work unchanged.  What differs is underneath:
 
 * everything but ``layer0`` (a 6 -> 128 torch addmm) goes through the C ABI of ``libpointdsc_b200.so`` (hand-written
-  sm_100a kernels): per encoder layer PointCN (``pdsc_mlp_chain``, BatchNorm folded), the q/k/v projections written
-  straight into the attention operand tiles (``pdsc_qkv_pack``), the compatibility-weighted attention without the
-  N x N matrix, and fc_message + residual (``pdsc_mlp_chain``); then the normalisation + classifier head, NMS seed
+  sm_100a kernels): per encoder layer the q/k/v projections written straight into the attention operand tiles
+  (``pdsc_qkv_pack``), the compatibility-weighted attention without the N x N matrix, and fc_message + residual joined
+  with the NEXT layer's PointCN in one launch (``pdsc_mlp_chain_direct``, BatchNorm folded; ``pdsc_mlp_chain`` for the
+  first PointCN and the last fc_message; ``join_layers=False`` / ``POINTDSC_JOIN_LAYERS=0`` selects the two-launch form,
+  bit-identical); then the normalisation + classifier head, NMS seed
   picking, seed-row feature kNN, per-seed spectral matching + Kabsch, hypothesis scoring and the whole post-refinement
   loop.  ``POINTDSC_MLP_MODE=split16|fp32`` keeps the 1x1 convs as torch GEMMs (the form BASELINE.json's north_star
   names).  There is no CPU or pure-PyTorch fallback: inputs must be CUDA tensors.
