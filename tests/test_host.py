@@ -117,6 +117,8 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     assert lib.pdsc_pick_seeds(None, None, 1, 10, 0.1, 1, None, None, None, None, 0, None) == 1
     assert lib.pdsc_feature_head(None, 10, 128, 32, 32, None, None, None, None, None, None, 1e-12, None, None, None) == 1
     assert b"feature_head" in lib.pdsc_last_error()
+    assert lib.pdsc_mlp_chain_direct(None, 10, 4, None, None, None, None, None, 2, None, None) == 1
+    assert b"mlp_chain_direct" in lib.pdsc_last_error()
 
 
 def test_front_end_and_icp_refuse_cpu_tensors():
