@@ -121,6 +121,24 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     assert b"mlp_chain_direct" in lib.pdsc_last_error()
 
 
+def test_mlp_chain_direct_refuses_bad_chains_before_touching_the_device():
+    """Shape errors of pdsc_mlp_chain_direct are caught on the host (dims and relu are host arrays; the device pointers are
+    never dereferenced on these paths, so dummy aligned addresses do)."""
+    import ctypes
+    lib = _cabi.load()
+    I32 = ctypes.c_int32
+    def call(n_layers, dims, residual, residual_layer):
+        d = (I32 * len(dims))(*dims)
+        r = (I32 * max(1, n_layers))(*([1] * max(1, n_layers)))
+        return lib.pdsc_mlp_chain_direct(256, 10, n_layers, ctypes.cast(d, ctypes.c_void_p), ctypes.cast(r, ctypes.c_void_p), 512, 768,
+                                         residual, residual_layer, 1024, None)
+    assert call(5, [128] * 6, None, 0) == 1 and b"layers" in lib.pdsc_last_error()
+    assert call(0, [128], None, 0) == 1
+    assert call(2, [128, 96, 128], None, 0) == 1 and b"64 or 128" in lib.pdsc_last_error()
+    assert call(2, [128, 64, 128], 1280, 2) == 1 and b"residual layer" in lib.pdsc_last_error()
+    assert call(2, [128, 64, 128], 1281, 0) == 1 and b"aligned" in lib.pdsc_last_error()
+
+
 def test_front_end_and_icp_refuse_cpu_tensors():
     from pointdsc_b200 import benchmark_utils, frontend
     pts = torch.rand(50, 3, dtype=torch.float64)
