@@ -114,6 +114,29 @@ def test_joined_layer_chains_change_nothing():
         assert torch.equal(a[k], b[k]), k
 
 
+def test_graph_replay_equals_eager_forward():
+    """pointdsc_b200.graphed.GraphedForward: the whole forward captured once as a CUDA graph (no entry point allocates or
+    synchronises) and replayed on new inputs gives the eager results bit for bit."""
+    from pointdsc_b200.graphed import GraphedForward
+    meta, g = load_golden("g1_3dmatch_n1000_l12")
+    model, _ = golden_model(meta)
+    cfg = synth.CONFIGS["3dmatch"]
+    fwd = GraphedForward(model, 2, 1000)
+    for seeds in ([7, 8], [30, 31], [7, 8]):
+        batch = synth.make_batch(seeds, 1000, **cfg)
+        data = {k: batch[k].cuda() for k in ("corr_pos", "src_keypts", "tgt_keypts")}
+        eager = model(dict(data, testing=True))
+        res = fwd(data["corr_pos"], data["src_keypts"], data["tgt_keypts"])
+        torch.cuda.synchronize()
+        for k in ("confidence", "seeds", "inlier_count", "initial_trans", "final_trans", "final_labels"):
+            assert torch.equal(eager[k], res[k]), k
+        assert bool(res["finite"])
+    # pair seed 7 is the golden pair
+    assert_trans_close(res["final_trans"][0:1], g["final_trans"])
+    with pytest.raises(ValueError):
+        fwd(data["corr_pos"][:1], data["src_keypts"][:1], data["tgt_keypts"][:1])
+
+
 def test_batched_forward_equals_per_pair_runs():
     """[B,N,.] means B independent pairs (reference test path is batch-size 1)."""
     meta, g = load_golden("g0_3dmatch_n256_l2")
